@@ -1,0 +1,205 @@
+/*
+ * m3r_backends.h -- C ABI of the B200-native geometric backend (libm3r_b200.so).
+ *
+ * This is the drop-in boundary for the reference's one native extension,
+ * `mast3r_slam_backends` (pybind11 module, /root/reference/mast3r_slam/backend/src/gn.cpp:116-123,
+ * declarations in backend/include/gn.h).  Each entry point below is what a binding of the
+ * corresponding reference export would call; the reference interface it replaces is cited
+ * per function.  Plain pointers, sizes and scalars only: no torch types.
+ *
+ * Conventions
+ *  - every tensor argument is a DEVICE pointer to a dense row-major (contiguous) buffer on
+ *    the current CUDA device, laid out exactly as the reference's tensors are
+ *    (the reference checks contiguity only: gn.h:5, gn.cpp:14-21);
+ *  - inputs are borrowed for the duration of the call; outputs are caller-allocated;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
+ *    enqueued on it; no entry point synchronises the device or the stream;
+ *  - return value: M3R_OK (0) or an M3R_ERR_* code; m3r_last_error() gives the message of
+ *    the last failure on the calling thread.  Numerical failure of the Gauss-Newton linear
+ *    solve is NOT an error: the step is zero, as in the reference (gn_kernels.cu:147-150).
+ */
+#ifndef M3R_BACKENDS_H
+#define M3R_BACKENDS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M3R_ABI_VERSION 1
+
+#define M3R_OK 0
+#define M3R_ERR_INVALID_ARGUMENT 1
+#define M3R_ERR_CUDA 2
+#define M3R_ERR_UNSUPPORTED 3
+#define M3R_ERR_NO_MEMORY 4
+
+/* dtype codes for refine_matches descriptors (AT_DISPATCH_FLOATING_TYPES_AND_HALF,
+ * matching_kernels.cu:103) */
+#define M3R_DTYPE_F16 0
+#define M3R_DTYPE_F32 1
+#define M3R_DTYPE_F64 2
+
+/* Gauss-Newton residual kinds */
+#define M3R_GN_RAYS 0   /* ray_align_kernel,  gn_kernels.cu:813-1138  */
+#define M3R_GN_CALIB 1  /* calib_proj_kernel, gn_kernels.cu:1231-1543 */
+#define M3R_GN_POINTS 2 /* point_align_kernel, gn_kernels.cu:455-723  */
+
+int m3r_abi_version(void);
+const char *m3r_last_error(void);
+
+/* Number of kernels this library has launched in the calling process since load (all
+ * streams); bench.py reads it around the timed region for its `gpu_launches` claim. */
+uint64_t m3r_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------
+ * iter_proj -- replaces `iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter,
+ * lambda_init, cost_thresh) -> [p_new, converged]`  (gn.h:89-95, gn.cpp:84-99,
+ * matching_kernels.cu:119-316).
+ *   rays_img_with_grad [b,h,w,9] f32   unit ray (3) + d/du (3) + d/dv (3) per pixel
+ *   pts_3d_norm        [b,n,3]   f32   unit rays to match
+ *   p_init             [b,n,2]   f32   initial (u,v)
+ *   p_new              [b,n,2]   f32   out
+ *   converged          [b,n]     u8    out (torch.bool storage)
+ * `variant`: 0 = library default; other values select alternative kernels with identical
+ * results (used by the benchmarks).
+ * ------------------------------------------------------------------------------------- */
+int m3r_iter_proj(const float *rays_img_with_grad, const float *pts_3d_norm,
+                  const float *p_init, float *p_new, uint8_t *converged, int b, int h, int w,
+                  int n, int max_iter, float lambda_init, float cost_thresh, void *stream);
+int m3r_iter_proj_v(const float *rays_img_with_grad, const float *pts_3d_norm,
+                    const float *p_init, float *p_new, uint8_t *converged, int b, int h, int w,
+                    int n, int max_iter, float lambda_init, float cost_thresh, int variant,
+                    void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * refine_matches -- replaces `refine_matches(D11, D21, p1, radius, dilation_max) ->
+ * [p1_new]`  (gn.h:112-117, gn.cpp:101-114, matching_kernels.cu:25-116).
+ *   D11    [b,h,w,fdim]  dtype     descriptors of view 1
+ *   D21    [b,n,fdim]    dtype     descriptors of the query points
+ *   p1     [b,n,2]       i64       (u,v) from iter_proj
+ *   p1_new [b,n,2]       i64       out
+ * Scores are accumulated in `dtype` exactly as the reference does (for f16: every multiply
+ * and every add rounds to binary16), so the result is bit-exact with the reference.
+ * ------------------------------------------------------------------------------------- */
+int m3r_refine_matches(const void *D11, const void *D21, const int64_t *p1, int64_t *p1_new,
+                       int b, int h, int w, int n, int fdim, int dtype, int radius,
+                       int dilation_max, void *stream);
+int m3r_refine_matches_v(const void *D11, const void *D21, const int64_t *p1, int64_t *p1_new,
+                         int b, int h, int w, int n, int fdim, int dtype, int radius,
+                         int dilation_max, int variant, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Gauss-Newton on the Sim(3) keyframe graph.
+ *
+ * A workspace caches device scratch (per-edge blocks, the assembled system, index maps)
+ * across calls; create one per device and per host thread that calls the solver.
+ * ------------------------------------------------------------------------------------- */
+typedef struct m3r_gn_workspace m3r_gn_workspace;
+int m3r_gn_workspace_create(m3r_gn_workspace **out);
+void m3r_gn_workspace_destroy(m3r_gn_workspace *ws);
+
+/* Common tensor arguments (reference layouts, gn.h:22-87):
+ *   Twc         [N,8]   f32  in/out  (t xyz, q xyzw, s); rows in sorted-unique keyframe order
+ *   Xs          [N,n,3] f32          canonical pointmaps
+ *   Cs          [N,n,1] f32          confidences
+ *   ii, jj      [E]     i64          keyframe ids of each directed edge i->j
+ *   idx_ii2jj   [E,n]   i64          for point k of j, its match in i
+ *   valid_match [E,n,1] u8 (bool)
+ *   Q           [E,n,1] f32          match confidence
+ *   dx          [N-1,7] f32  out     step of the last executed iteration (tau, omega, sigma)
+ * Pose 0 is held fixed (num_fix = 1, gn_kernels.cu:741,1157,1566).  The loop runs up to
+ * max_iter iterations and stops after the first one whose ||dx||_F < delta_thresh
+ * (gn_kernels.cu:1219-1222); the test happens on the device, the call never blocks.
+ */
+
+/* replaces gauss_newton_rays (gn.h:45-55, gn.cpp:28-52, gn_kernels.cu:1140-1228) */
+int m3r_gauss_newton_rays(m3r_gn_workspace *ws, float *Twc, const float *Xs, const float *Cs,
+                          const int64_t *ii, const int64_t *jj, const int64_t *idx_ii2jj,
+                          const uint8_t *valid_match, const float *Q, float *dx, int num_poses,
+                          int num_points, int num_edges, float sigma_ray, float sigma_dist,
+                          float C_thresh, float Q_thresh, int max_iter, float delta_thresh,
+                          void *stream);
+
+/* replaces gauss_newton_calib (gn.h:74-87, gn.cpp:54-82, gn_kernels.cu:1546-1638);
+ * K is a DEVICE pointer to the [3,3] f32 intrinsics (fx=K[0], fy=K[4], cx=K[2], cy=K[5]) */
+int m3r_gauss_newton_calib(m3r_gn_workspace *ws, float *Twc, const float *Xs, const float *Cs,
+                           const float *K, const int64_t *ii, const int64_t *jj,
+                           const int64_t *idx_ii2jj, const uint8_t *valid_match, const float *Q,
+                           float *dx, int num_poses, int num_points, int num_edges, int height,
+                           int width, int pixel_border, float z_eps, float sigma_pixel,
+                           float sigma_depth, float C_thresh, float Q_thresh, int max_iter,
+                           float delta_thresh, void *stream);
+
+/* replaces gauss_newton_points (gn.h:22-31, gn.cpp:3-26, gn_kernels.cu:725-811) */
+int m3r_gauss_newton_points(m3r_gn_workspace *ws, float *Twc, const float *Xs, const float *Cs,
+                            const int64_t *ii, const int64_t *jj, const int64_t *idx_ii2jj,
+                            const uint8_t *valid_match, const float *Q, float *dx,
+                            int num_poses, int num_points, int num_edges, float sigma_point,
+                            float C_thresh, float Q_thresh, int max_iter, float delta_thresh,
+                            void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Staged Gauss-Newton (what the three calls above are made of).  Used by the multi-GPU
+ * path, where each rank linearises its own shard of the directed edges and the assembled
+ * systems are summed across ranks before every rank solves and retracts its replica of
+ * Twc, and by the parity tests, which check each stage against the oracle.
+ * ------------------------------------------------------------------------------------- */
+typedef struct {
+  int kind;                 /* M3R_GN_RAYS | M3R_GN_CALIB | M3R_GN_POINTS */
+  int num_poses;            /* N */
+  int num_points;           /* n */
+  int num_edges;            /* E: directed edges of the WHOLE graph (length of ii, jj) */
+  int edge_begin, edge_end; /* this call's shard [begin,end) of the directed edges */
+  float *Twc;               /* [N,8] in/out (replicated) */
+  const float *Xs;          /* [N,n,3] (replicated) */
+  const float *Cs;          /* [N,n]   (replicated) */
+  const int64_t *ii;        /* [E] whole graph */
+  const int64_t *jj;        /* [E] whole graph */
+  const int64_t *idx_ii2jj; /* [edge_end-edge_begin, n] rows of this shard only */
+  const uint8_t *valid_match; /* [edge_end-edge_begin, n] */
+  const float *Q;             /* [edge_end-edge_begin, n] */
+  /* residual parameters (unused ones ignored) */
+  float sigma_ray, sigma_dist;           /* rays   */
+  const float *K;                        /* calib: device [3,3] */
+  int height, width, pixel_border;       /* calib  */
+  float z_eps, sigma_pixel, sigma_depth; /* calib  */
+  float sigma_point;                     /* points */
+  float C_thresh, Q_thresh;
+} m3r_gn_problem;
+
+/* Size in doubles of the assembled system buffer: D*D (dense, row-major, lower triangle
+ * meaningful) followed by D right-hand-side entries, D = 7*(N-1). */
+int64_t m3r_gn_system_size(int num_poses);
+
+/* Resets the device-side stop flag and remaps keyframe ids to packed pose indices
+ * (replaces get_unique_kf_idx/create_inds, gn_kernels.cu:161-170, without the host sync). */
+int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, void *stream);
+
+/* One accumulation pass over the shard's edges and deterministic assembly into `system`
+ * (caller-allocated device buffer of m3r_gn_system_size doubles; fully overwritten). */
+int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob, double *system,
+                     void *stream);
+
+/* Cholesky-solve `system` (destroyed), dx = -H^{-1} b (zeros if the factorisation fails),
+ * left-retract poses 1..N-1 in place, set the stop flag if ||dx||_F < delta_thresh.
+ * After the stop flag is set, m3r_gn_linearize / m3r_gn_solve_retract become no-ops on the
+ * device, which is how the max_iter loop ends early without a host round trip. */
+int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *prob, double *system,
+                         float *dx, float delta_thresh, void *stream);
+
+/* Per-edge world-frame blocks of the last m3r_gn_linearize, for the parity tests:
+ * Hjj [E_shard,7,7] and gj [E_shard,7] in double, with H_ii = H_jj, H_ij = H_ji = -H_jj,
+ * g_i = -g_j (the identities the reference's Ji = -Jj implies, gn_kernels.cu:1000).
+ * Device pointers owned by the workspace, valid until the next call on it. */
+int m3r_gn_edge_blocks(m3r_gn_workspace *ws, const double **Hjj, const double **gj);
+
+/* Number of iterations the last m3r_gauss_newton_* / staged loop executed.  This call
+ * synchronises `stream` (it reads a device counter); it is for tests and benchmarks. */
+int m3r_gn_iterations_done(m3r_gn_workspace *ws, void *stream, int *iters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M3R_BACKENDS_H */

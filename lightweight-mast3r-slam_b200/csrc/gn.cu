@@ -1,0 +1,1206 @@
+// Sim(3) keyframe-graph Gauss-Newton for sm_100a: accumulation, deterministic assembly,
+// on-device fp64 Cholesky solve, left retraction and the stop test, with no host round trip.
+//
+// Replaces the reference's gn_kernels.cu (ray_align_kernel :813-1138, calib_proj_kernel
+// :1231-1543, point_align_kernel :455-723, pose_retr_kernel :415-453, the Eigen SparseBlock
+// host solve :57-159 and the three driver loops) behind include/m3r_backends.h.
+//
+// Design (not a translation of the reference):
+//  * The reference carries the full 14x14 packed Hessian of (pose i, pose j) per thread and
+//    maps every residual row into the world frame per point.  Its own Ji = -Jj
+//    (gn_kernels.cu:1000) means the 14x14 block is [[H,-H],[-H,H]] with H = A S A^T, where S
+//    is the 7x7 sum of w * J_loc^T J_loc in the LOCAL frame of camera i and A is the 7x7
+//    matrix of apply_Sim3_adj_inv(T_i) (:277-297), constant over the edge.  So the streaming
+//    kernel accumulates only S (28 values, sparsity of J_loc resolved at compile time) and
+//    s = sum w*e*J_loc (7 values); A is applied once per edge in fp64.
+//  * Work is split into (edge, chunk) items over a persistent grid; every item writes its
+//    partial sums to its own slot, and the chunk partials are combined in a fixed order in
+//    fp64: bitwise reproducible, no atomics.
+//  * Assembly into the dense lower-triangular system is a gather per 7x7 block pair over the
+//    edge list in edge order (deterministic).  The system is factored by a blocked fp64
+//    Cholesky on the device; failure (non-positive pivot) yields dx = 0 as in :147-150.
+//  * Retraction, ||dx|| and the stop flag live in the same final kernel; once the flag is set
+//    the remaining enqueued kernels exit at their first instruction.
+#include "m3r_common.cuh"
+
+namespace m3r {
+
+// ----------------------------------------------------------------------------------------
+// small math
+// ----------------------------------------------------------------------------------------
+struct Pose {
+  float t[3], q[4], s;
+};
+
+__device__ __forceinline__ Pose load_pose(const float *__restrict__ Twc, int k) {
+  Pose P;
+  const float4 a = *reinterpret_cast<const float4 *>(Twc + k * 8);
+  const float4 b = *reinterpret_cast<const float4 *>(Twc + k * 8 + 4);
+  P.t[0] = a.x, P.t[1] = a.y, P.t[2] = a.z;
+  P.q[0] = a.w, P.q[1] = b.x, P.q[2] = b.y, P.q[3] = b.z;
+  P.s = b.w;
+  return P;
+}
+
+template <typename T>
+__device__ __forceinline__ void act_so3(const T q[4], const T X[3], T Y[3]) {
+  // gn_kernels.cu:195-205
+  const T uv0 = T(2) * (q[1] * X[2] - q[2] * X[1]);
+  const T uv1 = T(2) * (q[2] * X[0] - q[0] * X[2]);
+  const T uv2 = T(2) * (q[0] * X[1] - q[1] * X[0]);
+  const T y0 = X[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1);
+  const T y1 = X[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2);
+  const T y2 = X[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0);
+  Y[0] = y0, Y[1] = y1, Y[2] = y2;
+}
+
+__device__ __forceinline__ void quat_mul(const float a[4], const float b[4], float o[4]) {
+  // gn_kernels.cu:178-184
+  o[0] = a[3] * b[0] + a[0] * b[3] + a[1] * b[2] - a[2] * b[1];
+  o[1] = a[3] * b[1] - a[0] * b[2] + a[1] * b[3] + a[2] * b[0];
+  o[2] = a[3] * b[2] + a[0] * b[1] - a[1] * b[0] + a[2] * b[3];
+  o[3] = a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2];
+}
+
+// T_ij = T_i^-1 T_j  (relSim3, gn_kernels.cu:252-272)
+__device__ __forceinline__ Pose rel_sim3(const Pose &Ti, const Pose &Tj) {
+  Pose R;
+  const float si_inv = __frcp_rn(Ti.s);
+  R.s = si_inv * Tj.s;
+  const float qi_inv[4] = {-Ti.q[0], -Ti.q[1], -Ti.q[2], Ti.q[3]};
+  quat_mul(qi_inv, Tj.q, R.q);
+  float d[3] = {Tj.t[0] - Ti.t[0], Tj.t[1] - Ti.t[1], Tj.t[2] - Ti.t[2]};
+  act_so3<float>(qi_inv, d, d);
+  R.t[0] = d[0] * si_inv, R.t[1] = d[1] * si_inv, R.t[2] = d[2] * si_inv;
+  return R;
+}
+
+__device__ __forceinline__ void act_sim3(const Pose &T, const float X[3], float Y[3]) {
+  // gn_kernels.cu:207-219
+  act_so3<float>(T.q, X, Y);
+  Y[0] = Y[0] * T.s + T.t[0];
+  Y[1] = Y[1] * T.s + T.t[1];
+  Y[2] = Y[2] * T.s + T.t[2];
+}
+
+__device__ __forceinline__ float huber_w(float r) {
+  // gn_kernels.cu:172-175 (k = 1.345)
+  const float a = fabsf(r);
+  return a < 1.345f ? 1.0f : __fdividef(1.345f, a);
+}
+
+// ----------------------------------------------------------------------------------------
+// local-frame accumulators: S (packed lower 7x7, index a*(a+1)/2 + c, a >= c) and s (7)
+// ----------------------------------------------------------------------------------------
+constexpr int kNS = 28;       // packed S
+constexpr int kNAcc = 35;     // S + s
+
+// Adds one residual row with weight w, error e and local Jacobian J.  MASK has bit a set when
+// J[a] can be non-zero; everything else is removed at compile time (adding an exact zero
+// product never changes a sum, so this is value-identical to the dense update).
+template <unsigned MASK>
+__device__ __forceinline__ void add_row(float w, float e, const float J[7], float acc[kNAcc]) {
+  const float we = w * e;
+#pragma unroll
+  for (int a = 0; a < 7; a++) {
+    if (!((MASK >> a) & 1u)) continue;
+    const float wa = w * J[a];
+#pragma unroll
+    for (int c = 0; c <= a; c++) {
+      if (!((MASK >> c) & 1u)) continue;
+      acc[a * (a + 1) / 2 + c] = fmaf(wa, J[c], acc[a * (a + 1) / 2 + c]);
+    }
+    acc[kNS + a] = fmaf(we, J[a], acc[kNS + a]);
+  }
+}
+
+struct GnParams {
+  float sigma_a_inv;  // rays: 1/sigma_ray   calib: 1/sigma_pixel  points: 1/sigma_point
+  float sigma_b_inv;  // rays: 1/sigma_dist  calib: 1/sigma_depth
+  float C_thresh, Q_thresh;
+  float fx, fy, cx, cy;  // calib (read on device from K)
+  int width, height;
+  float u_lo, u_hi, v_lo, v_hi;  // calib: pixel_border bounds as floats
+  float z_eps;
+};
+
+template <int KIND>
+struct Residual;
+
+// ray_align_kernel :910-1090 -- residual (unit-ray difference, distance difference)
+template <>
+struct Residual<M3R_GN_RAYS> {
+  static __device__ __forceinline__ void point(const GnParams &P, const Pose &Tij,
+                                               const float Xi[3], const float Xj[3], float q,
+                                               long long, float acc[kNAcc]) {
+    const float n2i = Xi[0] * Xi[0] + Xi[1] * Xi[1] + Xi[2] * Xi[2];
+    const float n1i = sqrtf(n2i);
+    const float n1i_inv = __frcp_rn(n1i);
+    float Pj[3];
+    act_sim3(Tij, Xj, Pj);
+    const float n2j = Pj[0] * Pj[0] + Pj[1] * Pj[1] + Pj[2] * Pj[2];
+    const float n1j = sqrtf(n2j);
+    const float n1j_inv = __frcp_rn(n1j);
+    const float r[3] = {n1j_inv * Pj[0], n1j_inv * Pj[1], n1j_inv * Pj[2]};
+    const float e0 = r[0] - n1i_inv * Xi[0];
+    const float e1 = r[1] - n1i_inv * Xi[1];
+    const float e2 = r[2] - n1i_inv * Xi[2];
+    const float e3 = n1j - n1i;
+    const float sq = sqrtf(q);
+    const float swr = P.sigma_a_inv * sq;
+    const float swd = P.sigma_b_inv * sq;
+    const float wr = swr * swr, wd = swd * swd;
+    const float w0 = huber_w(swr * e0) * wr;
+    const float w1 = huber_w(swr * e1) * wr;
+    const float w2 = huber_w(swr * e2) * wr;
+    const float w3 = huber_w(swd * e3) * wd;
+    const float n3 = __fdividef(n1j_inv, n2j);  // 1/|P|^3 (:982)
+    const float axx = n1j_inv - Pj[0] * Pj[0] * n3;
+    const float ayy = n1j_inv - Pj[1] * Pj[1] * n3;
+    const float azz = n1j_inv - Pj[2] * Pj[2] * n3;
+    const float axy = -Pj[0] * Pj[1] * n3;
+    const float axz = -Pj[0] * Pj[2] * n3;
+    const float ayz = -Pj[1] * Pj[2] * n3;
+    {
+      const float J[7] = {axx, axy, axz, 0.f, r[2], -r[1], 0.f};  // :991-997
+      add_row<0b0110111>(w0, e0, J, acc);
+    }
+    {
+      const float J[7] = {axy, ayy, ayz, -r[2], 0.f, r[0], 0.f};  // :1016-1022
+      add_row<0b0101111>(w1, e1, J, acc);
+    }
+    {
+      const float J[7] = {axz, ayz, azz, r[1], -r[0], 0.f, 0.f};  // :1041-1047
+      add_row<0b0011111>(w2, e2, J, acc);
+    }
+    {
+      const float J[7] = {r[0], r[1], r[2], 0.f, 0.f, 0.f, n1j};  // :1067-1073
+      add_row<0b1000111>(w3, e3, J, acc);
+    }
+  }
+  static __device__ __forceinline__ bool extra_valid(const GnParams &, const Pose &,
+                                                     const float *, const float *) {
+    return true;
+  }
+};
+
+// point_align_kernel :550-677 -- residual X_j->i - X_i
+template <>
+struct Residual<M3R_GN_POINTS> {
+  static __device__ __forceinline__ void point(const GnParams &P, const Pose &Tij,
+                                               const float Xi[3], const float Xj[3], float q,
+                                               long long, float acc[kNAcc]) {
+    float Pj[3];
+    act_sim3(Tij, Xj, Pj);
+    const float e0 = Pj[0] - Xi[0], e1 = Pj[1] - Xi[1], e2 = Pj[2] - Xi[2];
+    const float sw = P.sigma_a_inv * sqrtf(q);
+    const float wc = sw * sw;
+    const float w0 = huber_w(sw * e0) * wc;
+    const float w1 = huber_w(sw * e1) * wc;
+    const float w2 = huber_w(sw * e2) * wc;
+    {
+      const float J[7] = {1.f, 0.f, 0.f, 0.f, Pj[2], -Pj[1], Pj[0]};  // :602-608
+      add_row<0b1110001>(w0, e0, J, acc);
+    }
+    {
+      const float J[7] = {0.f, 1.f, 0.f, -Pj[2], 0.f, Pj[0], Pj[1]};  // :627-633
+      add_row<0b1101010>(w1, e1, J, acc);
+    }
+    {
+      const float J[7] = {0.f, 0.f, 1.f, Pj[1], -Pj[0], 0.f, Pj[2]};  // :652-658
+      add_row<0b1011100>(w2, e2, J, acc);
+    }
+  }
+};
+
+// calib_proj_kernel :1346-1497 -- residual (pixel u, pixel v, log depth)
+template <>
+struct Residual<M3R_GN_CALIB> {
+  static __device__ __forceinline__ void point(const GnParams &P, const Pose &Tij,
+                                               const float Xi[3], const float Xj[3], float q,
+                                               long long ind_Xi, float acc[kNAcc]) {
+    float Pj[3];
+    act_sim3(Tij, Xj, Pj);
+    const bool valid_z = (Pj[2] > P.z_eps) && (Xi[2] > P.z_eps);  // :1368
+    if (!valid_z) return;
+    const float iz = __frcp_rn(Pj[2]);
+    const float x = Pj[0] * iz, y = Pj[1] * iz;
+    const float u = P.fx * x + P.cx;
+    const float v = P.fy * y + P.cy;
+    const bool valid_uv = (u > P.u_lo) && (u < P.u_hi) && (v > P.v_lo) && (v < P.v_hi);  // :1382-1383
+    if (!valid_uv) return;
+    const int u_t = static_cast<int>(ind_Xi % P.width);  // :1361-1362
+    const int v_t = static_cast<int>(ind_Xi / P.width);
+    const float e0 = u - static_cast<float>(u_t);
+    const float e1 = v - static_cast<float>(v_t);
+    const float e2 = logf(Pj[2]) - logf(Xi[2]);
+    const float sq = sqrtf(q);
+    const float swp = P.sigma_a_inv * sq;
+    const float swd = P.sigma_b_inv * sq;
+    const float wp = swp * swp, wd = swd * swd;
+    const float w0 = huber_w(swp * e0) * wp;
+    const float w1 = huber_w(swp * e1) * wp;
+    const float w2 = huber_w(swd * e2) * wd;
+    {
+      const float J[7] = {P.fx * iz,       0.f, -P.fx * x * iz, -P.fx * x * y,
+                          P.fx * (1.f + x * x), -P.fx * y,      0.f};  // :1422-1428
+      add_row<0b0111101>(w0, e0, J, acc);
+    }
+    {
+      const float J[7] = {0.f,          P.fy * iz, -P.fy * y * iz, -P.fy * (1.f + y * y),
+                          P.fy * x * y, P.fy * x,  0.f};  // :1448-1454
+      add_row<0b0111110>(w1, e1, J, acc);
+    }
+    {
+      const float J[7] = {0.f, 0.f, iz, y, -x, 0.f, 1.f};  // :1473-1479
+      add_row<0b1011100>(w2, e2, J, acc);
+    }
+  }
+};
+
+// ----------------------------------------------------------------------------------------
+// accumulation kernel
+// ----------------------------------------------------------------------------------------
+constexpr int kAccThreads = 256;
+constexpr int kAccWarps = kAccThreads / 32;
+constexpr int kChunk = 8192;  // points per work item (multiple of 4*kAccThreads)
+
+struct AccArgs {
+  const float *Twc;
+  const float *Xs;
+  const float *Cs;
+  const long long *idx;        // shard rows
+  const unsigned char *valid;  // shard rows
+  const float *Q;              // shard rows
+  const int *pose_i;           // [E] whole graph, packed pose index
+  const int *pose_j;
+  const float *K;              // calib
+  double *partials;            // [items, 35]
+  const int *flags;
+  int n, edge_begin, num_shard_edges, chunks_per_edge;
+  GnParams P;
+};
+
+__device__ __forceinline__ float4 ldcs4(const float *p) {
+  return __ldcs(reinterpret_cast<const float4 *>(p));
+}
+
+template <int KIND, int VEC>
+__global__ void __launch_bounds__(kAccThreads, 2) gn_accumulate_kernel(const AccArgs A) {
+  if (A.flags[0]) return;  // converged earlier: nothing to do
+  __shared__ double red[kAccWarps][kNAcc];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n = A.n;
+  const int items = A.num_shard_edges * A.chunks_per_edge;
+
+  GnParams P = A.P;
+  if (KIND == M3R_GN_CALIB) {  // intrinsics live on the device (gn_kernels.cu:1274-1279)
+    P.fx = __ldg(A.K + 0), P.fy = __ldg(A.K + 4), P.cx = __ldg(A.K + 2), P.cy = __ldg(A.K + 5);
+  }
+
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int le = item / A.chunks_per_edge;  // edge within the shard
+    const int ch = item - le * A.chunks_per_edge;
+    const int e = A.edge_begin + le;
+    const int ix = A.pose_i[e], jx = A.pose_j[e];
+    const Pose Ti = load_pose(A.Twc, ix);
+    const Pose Tj = load_pose(A.Twc, jx);
+    const Pose Tij = rel_sim3(Ti, Tj);
+
+    const float *Xi_base = A.Xs + static_cast<size_t>(ix) * n * 3;
+    const float *Xj_base = A.Xs + static_cast<size_t>(jx) * n * 3;
+    const float *Ci_base = A.Cs + static_cast<size_t>(ix) * n;
+    const float *Cj_base = A.Cs + static_cast<size_t>(jx) * n;
+    const long long *idx_e = A.idx + static_cast<size_t>(le) * n;
+    const unsigned char *val_e = A.valid + static_cast<size_t>(le) * n;
+    const float *Q_e = A.Q + static_cast<size_t>(le) * n;
+
+    float acc[kNAcc];
+#pragma unroll
+    for (int k = 0; k < kNAcc; k++) acc[k] = 0.f;
+
+    const int k_begin = ch * kChunk;
+    const int k_end = min(n, k_begin + kChunk);
+    for (int k0 = k_begin + threadIdx.x * VEC; k0 < k_end; k0 += kAccThreads * VEC) {
+      float Xj[VEC][3], qv[VEC], cj[VEC];
+      long long id[VEC];
+      unsigned char vm[VEC];
+      if (VEC == 4) {
+        const float4 a = __ldg(reinterpret_cast<const float4 *>(Xj_base + static_cast<size_t>(k0) * 3));
+        const float4 b = __ldg(reinterpret_cast<const float4 *>(Xj_base + static_cast<size_t>(k0) * 3 + 4));
+        const float4 c = __ldg(reinterpret_cast<const float4 *>(Xj_base + static_cast<size_t>(k0) * 3 + 8));
+        Xj[0][0] = a.x, Xj[0][1] = a.y, Xj[0][2] = a.z;
+        Xj[1 % VEC][0] = a.w, Xj[1 % VEC][1] = b.x, Xj[1 % VEC][2] = b.y;
+        Xj[2 % VEC][0] = b.z, Xj[2 % VEC][1] = b.w, Xj[2 % VEC][2] = c.x;
+        Xj[3 % VEC][0] = c.y, Xj[3 % VEC][1] = c.z, Xj[3 % VEC][2] = c.w;
+        const float4 qq = ldcs4(Q_e + k0);
+        qv[0] = qq.x, qv[1 % VEC] = qq.y, qv[2 % VEC] = qq.z, qv[3 % VEC] = qq.w;
+        const float4 cc = __ldg(reinterpret_cast<const float4 *>(Cj_base + k0));
+        cj[0] = cc.x, cj[1 % VEC] = cc.y, cj[2 % VEC] = cc.z, cj[3 % VEC] = cc.w;
+        const longlong2 i0 = __ldcs(reinterpret_cast<const longlong2 *>(idx_e + k0));
+        const longlong2 i1 = __ldcs(reinterpret_cast<const longlong2 *>(idx_e + k0 + 2));
+        id[0] = i0.x, id[1 % VEC] = i0.y, id[2 % VEC] = i1.x, id[3 % VEC] = i1.y;
+        const uchar4 vv = __ldcs(reinterpret_cast<const uchar4 *>(val_e + k0));
+        vm[0] = vv.x, vm[1 % VEC] = vv.y, vm[2 % VEC] = vv.z, vm[3 % VEC] = vv.w;
+      } else {
+#pragma unroll
+        for (int p = 0; p < VEC; p++) {
+          const int k = k0 + p;
+          Xj[p][0] = __ldg(Xj_base + static_cast<size_t>(k) * 3 + 0);
+          Xj[p][1] = __ldg(Xj_base + static_cast<size_t>(k) * 3 + 1);
+          Xj[p][2] = __ldg(Xj_base + static_cast<size_t>(k) * 3 + 2);
+          qv[p] = __ldcs(Q_e + k);
+          cj[p] = __ldg(Cj_base + k);
+          id[p] = __ldcs(idx_e + k);
+          vm[p] = __ldcs(val_e + k);
+        }
+      }
+      // gathers from keyframe i (:914-918, :951): invalid matches read point 0, as the
+      // reference does, but the loads are only issued for points that can contribute
+      float Xi[VEC][3], ci[VEC];
+      bool ok[VEC];
+#pragma unroll
+      for (int p = 0; p < VEC; p++) {
+        ok[p] = (vm[p] != 0) && (qv[p] > P.Q_thresh) && (cj[p] > P.C_thresh);
+        // clamp keeps a corrupt index from reading outside keyframe i's pointmap
+        const long long ii = ok[p] ? min(max(id[p], 0LL), static_cast<long long>(n - 1)) : 0LL;
+        id[p] = ii;
+        Xi[p][0] = __ldg(Xi_base + ii * 3 + 0);
+        Xi[p][1] = __ldg(Xi_base + ii * 3 + 1);
+        Xi[p][2] = __ldg(Xi_base + ii * 3 + 2);
+        ci[p] = __ldg(Ci_base + ii);
+      }
+#pragma unroll
+      for (int p = 0; p < VEC; p++) {
+        if (ok[p] && ci[p] > P.C_thresh)
+          Residual<KIND>::point(P, Tij, Xi[p], Xj[p], qv[p], id[p], acc);
+      }
+    }
+
+    // warp tree in fp32, then fp64 across warps in a fixed order
+#pragma unroll
+    for (int k = 0; k < kNAcc; k++) {
+      float v = acc[k];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+      if (lane == 0) red[warp][k] = static_cast<double>(v);
+    }
+    __syncthreads();
+    if (threadIdx.x < kNAcc) {
+      double s = 0.0;
+#pragma unroll
+      for (int wq = 0; wq < kAccWarps; wq++) s += red[wq][threadIdx.x];
+      A.partials[static_cast<size_t>(item) * kNAcc + threadIdx.x] = s;
+    }
+    __syncthreads();
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// per-edge finalisation: S = sum of chunk partials (fixed order), H_jj = A S A^T, g_j = A s
+// ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64)
+    gn_edge_finalize_kernel(const double *__restrict__ partials, const float *__restrict__ Twc,
+                            const int *__restrict__ pose_i, int edge_begin, int chunks_per_edge,
+                            double *__restrict__ edge_H, double *__restrict__ edge_g,
+                            const int *__restrict__ flags) {
+  if (flags[0]) return;
+  __shared__ double S[7][7], sv[7], Am[7][7], AS[7][7];
+  const int le = blockIdx.x;
+  const int t = threadIdx.x;
+  if (t < kNAcc) {
+    double s = 0.0;
+    for (int c = 0; c < chunks_per_edge; c++)
+      s += partials[(static_cast<size_t>(le) * chunks_per_edge + c) * kNAcc + t];
+    if (t < kNS) {
+      int a = 0;
+      while ((a + 1) * (a + 2) / 2 <= t) a++;
+      const int c = t - a * (a + 1) / 2;
+      S[a][c] = s;
+      S[c][a] = s;
+    } else {
+      sv[t - kNS] = s;
+    }
+  }
+  if (t == 63) {
+    // A = matrix of apply_Sim3_adj_inv(T_i) (gn_kernels.cu:277-297):
+    //   Y[0:3] = R a / s,  Y[3:6] = R b + t x (R a) / s,  Y[6] = c + t . (R a) / s
+    const int ix = pose_i[edge_begin + le];
+    const float *Pp = Twc + ix * 8;
+    const double tt[3] = {Pp[0], Pp[1], Pp[2]};
+    const double q[4] = {Pp[3], Pp[4], Pp[5], Pp[6]};
+    const double s_inv = 1.0 / static_cast<double>(Pp[7]);
+    for (int r = 0; r < 7; r++)
+      for (int c = 0; c < 7; c++) Am[r][c] = 0.0;
+    for (int c = 0; c < 3; c++) {
+      double ex[3] = {0, 0, 0}, Rc[3];
+      ex[c] = 1.0;
+      act_so3<double>(q, ex, Rc);  // column c of R
+      for (int r = 0; r < 3; r++) {
+        Am[r][c] = s_inv * Rc[r];
+        Am[3 + r][3 + c] = Rc[r];
+      }
+      Am[3][c] = s_inv * (tt[1] * Rc[2] - tt[2] * Rc[1]);
+      Am[4][c] = s_inv * (tt[2] * Rc[0] - tt[0] * Rc[2]);
+      Am[5][c] = s_inv * (tt[0] * Rc[1] - tt[1] * Rc[0]);
+      Am[6][c] = s_inv * (tt[0] * Rc[0] + tt[1] * Rc[1] + tt[2] * Rc[2]);
+    }
+    Am[6][6] = 1.0;
+  }
+  __syncthreads();
+  if (t < 49) {
+    const int r = t / 7, c = t % 7;
+    double v = 0.0;
+    for (int k = 0; k < 7; k++) v += Am[r][k] * S[k][c];
+    AS[r][c] = v;
+  }
+  __syncthreads();
+  if (t < 49) {
+    const int r = t / 7, c = t % 7;
+    if (r >= c) {  // compute the lower triangle, mirror: exactly symmetric blocks
+      double v = 0.0;
+      for (int k = 0; k < 7; k++) v += AS[r][k] * Am[c][k];
+      edge_H[static_cast<size_t>(le) * 49 + r * 7 + c] = v;
+      edge_H[static_cast<size_t>(le) * 49 + c * 7 + r] = v;
+    }
+  } else if (t < 56) {
+    const int r = t - 49;
+    double v = 0.0;
+    for (int k = 0; k < 7; k++) v += Am[r][k] * sv[k];
+    edge_g[static_cast<size_t>(le) * 7 + r] = v;
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// deterministic assembly of the dense system  (SparseBlock::update_lhs/update_rhs, :71-113)
+//   block (a,b), a >= b, of H (D x D row-major, D = 7*(N-1)); pose p -> block p-1, pose 0 fixed
+//   H[a][a] += H_e for every edge touching a;  H[a][b] -= H_e for every edge joining a and b
+//   rhs[a]  += g_e (a = j side) or -g_e (a = i side)
+// ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64)
+    gn_assemble_kernel(const double *__restrict__ edge_H, const double *__restrict__ edge_g,
+                       const int *__restrict__ pose_i, const int *__restrict__ pose_j,
+                       int edge_begin, int num_shard_edges, int NB, double *__restrict__ sys,
+                       const int *__restrict__ flags) {
+  if (flags[0]) return;
+  const int a = blockIdx.y, b = blockIdx.x;  // block row, block col
+  const int t = threadIdx.x;
+  const int D = NB * 7;
+  const int r = t / 7, c = t % 7;
+  if (a < b) {  // strictly upper blocks are never read; keep them zero for the all-reduce
+    if (t < 49) sys[static_cast<size_t>(a * 7 + r) * D + (b * 7 + c)] = 0.0;
+    return;
+  }
+  __shared__ int hit[64];
+  __shared__ int nhit;
+  double accH = 0.0, accg = 0.0;
+  for (int e0 = 0; e0 < num_shard_edges; e0 += 64) {
+    const int le = e0 + t;
+    int code = 0;  // 1: +H (diag, i side)  2: +H (diag, j side)  3: -H (off-diagonal)
+    if (le < num_shard_edges) {
+      const int io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;
+      if (a == b) {
+        if (io == a && jo == a) code = 0;  // self edge: the four blocks cancel exactly
+        else if (io == a) code = 1;
+        else if (jo == a) code = 2;
+      } else if ((io == a && jo == b) || (io == b && jo == a)) {
+        code = 3;
+      }
+    }
+    // compact the hits of this tile in edge order
+    const unsigned m0 = __ballot_sync(0xffffffffu, code != 0);
+    __shared__ unsigned masks[2];
+    if ((t & 31) == 0) masks[t >> 5] = m0;
+    __syncthreads();
+    const unsigned lo = masks[0], hi = masks[1];
+    if (code != 0) {
+      const int pos = (t < 32) ? __popc(lo & ((1u << t) - 1u))
+                               : __popc(lo) + __popc(hi & ((1u << (t - 32)) - 1u));
+      hit[pos] = (le << 2) | code;
+    }
+    if (t == 0) nhit = __popc(lo) + __popc(hi);
+    __syncthreads();
+    const int nh = nhit;
+    for (int k = 0; k < nh; k++) {
+      const int hle = hit[k] >> 2, hc = hit[k] & 3;
+      if (t < 49) {
+        const double v = edge_H[static_cast<size_t>(hle) * 49 + t];
+        accH += (hc == 3) ? -v : v;
+      } else if (t < 56 && a == b) {
+        const double g = edge_g[static_cast<size_t>(hle) * 7 + (t - 49)];
+        accg += (hc == 1) ? -g : g;  // g_i = -g_j
+      }
+    }
+    __syncthreads();
+  }
+  if (t < 49) sys[static_cast<size_t>(a * 7 + r) * D + (b * 7 + c)] = accH;
+  else if (t < 56 && a == b) sys[static_cast<size_t>(D) * D + a * 7 + (t - 49)] = accg;
+}
+
+// ----------------------------------------------------------------------------------------
+// blocked Cholesky (fp64, lower, in place, row-major with leading dimension D)
+// ----------------------------------------------------------------------------------------
+constexpr int kPB = 32;  // panel width
+
+// Factor the kPB x kPB diagonal block at k0 in shared memory (every CTA does it redundantly,
+// it is 11k flops), then solve this CTA's 64 rows of the panel: L21 = A21 L11^-T.
+// CTA 0 also stores L11.
+// L11 goes to `ldiag` (panel-major [D/kPB][kPB][kPB]) rather than back into the matrix: the
+// other CTAs of this launch are still reading the unfactored block from there.
+__global__ void __launch_bounds__(64)
+    chol_panel_kernel(double *__restrict__ Amat, double *__restrict__ ldiag, int D, int k0,
+                      int *__restrict__ flags) {
+  if (flags[0]) return;
+  __shared__ double L[kPB][kPB + 1];
+  const int t = threadIdx.x;
+  const int pb = min(kPB, D - k0);
+  for (int x = t; x < kPB * kPB; x += 64) {
+    const int r = x / kPB, c = x % kPB;
+    L[r][c] = (r < pb && c <= r) ? Amat[static_cast<size_t>(k0 + r) * D + (k0 + c)] : 0.0;
+  }
+  __syncthreads();
+  __shared__ int bad;
+  if (t == 0) bad = 0;
+  for (int j = 0; j < pb; j++) {
+    __syncthreads();
+    if (t == 0) {
+      const double d = L[j][j];
+      if (!(d > 0.0)) {
+        bad = 1;
+        L[j][j] = 1.0;  // keep going with finite numbers; the result is discarded
+      } else {
+        L[j][j] = sqrt(d);
+      }
+    }
+    __syncthreads();
+    const double inv = 1.0 / L[j][j];
+    for (int r = j + 1 + t; r < pb; r += 64) L[r][j] *= inv;
+    __syncthreads();
+    // trailing update of the small block: rows r > j, cols j < c <= r
+    for (int x = t; x < (pb - j - 1) * (pb - j - 1); x += 64) {
+      const int r = j + 1 + x / (pb - j - 1), c = j + 1 + x % (pb - j - 1);
+      if (c <= r) L[r][c] -= L[r][j] * L[c][j];
+    }
+  }
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    if (t == 0 && bad) flags[2] = 1;
+    double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kPB * kPB;
+    for (int x = t; x < kPB * kPB; x += 64) Ld[x] = L[x / kPB][x % kPB];
+  }
+  // rows below the diagonal block: one row per thread, forward substitution against L11
+  const int row = k0 + pb + blockIdx.x * 64 + t;
+  if (row < D) {
+    double x[kPB];
+    double *Ar = Amat + static_cast<size_t>(row) * D + k0;
+#pragma unroll
+    for (int c = 0; c < kPB; c++) x[c] = (c < pb) ? Ar[c] : 0.0;
+#pragma unroll
+    for (int c = 0; c < kPB; c++) {
+      if (c < pb) {
+        double s = x[c];
+#pragma unroll
+        for (int k = 0; k < kPB; k++)
+          if (k < c) s -= x[k] * L[c][k];
+        x[c] = s / L[c][c];
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kPB; c++)
+      if (c < pb) Ar[c] = x[c];
+  }
+}
+
+// A22 -= L21 L21^T on the lower 64x64 tiles of the trailing matrix.
+__global__ void __launch_bounds__(256)
+    chol_update_kernel(double *__restrict__ Amat, int D, int k0, const int *__restrict__ flags) {
+  if (flags[0]) return;
+  const int tr = blockIdx.y, tc = blockIdx.x;
+  if (tc > tr) return;
+  const int base = k0 + kPB;
+  __shared__ double Ra[64][kPB + 1], Rb[64][kPB + 1];
+  const int t = threadIdx.x;
+  for (int x = t; x < 64 * kPB; x += 256) {
+    const int r = x / kPB, c = x % kPB;
+    const int ga = base + tr * 64 + r, gb = base + tc * 64 + r;
+    Ra[r][c] = (ga < D) ? Amat[static_cast<size_t>(ga) * D + k0 + c] : 0.0;
+    Rb[r][c] = (gb < D) ? Amat[static_cast<size_t>(gb) * D + k0 + c] : 0.0;
+  }
+  __syncthreads();
+  const int ty = t / 16, tx = t % 16;  // 16x16 threads, 4x4 outputs each
+  double acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
+#pragma unroll 8
+  for (int k = 0; k < kPB; k++) {
+    double av[4], bv[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) av[i] = Ra[ty + 16 * i][k], bv[i] = Rb[tx + 16 * i][k];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[i][j] += av[i] * bv[j];
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int gr = base + tr * 64 + ty + 16 * i, gc = base + tc * 64 + tx + 16 * j;
+      if (gr < D && gc <= gr) Amat[static_cast<size_t>(gr) * D + gc] -= acc[i][j];
+    }
+}
+
+// ----------------------------------------------------------------------------------------
+// triangular solves, dx = -x, retraction, stop test (one CTA)
+// ----------------------------------------------------------------------------------------
+__device__ void exp_so3(const float phi[3], float q[4]) {
+  // gn_kernels.cu:299-321
+  const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+  float imag, real;
+  if (theta_sq < 1e-6f) {
+    const float theta_p4 = theta_sq * theta_sq;
+    imag = 0.5f - (1.0f / 48.0f) * theta_sq + (1.0f / 3840.0f) * theta_p4;
+    real = 1.0f - (1.0f / 8.0f) * theta_sq + (1.0f / 384.0f) * theta_p4;
+  } else {
+    const float theta = sqrtf(theta_sq);
+    imag = sinf(0.5f * theta) / theta;
+    real = cosf(0.5f * theta);
+  }
+  q[0] = imag * phi[0], q[1] = imag * phi[1], q[2] = imag * phi[2], q[3] = real;
+}
+
+__device__ __forceinline__ void cross_inplace(const float a[3], float b[3]) {
+  const float x0 = a[1] * b[2] - a[2] * b[1];
+  const float x1 = a[2] * b[0] - a[0] * b[2];
+  const float x2 = a[0] * b[1] - a[1] * b[0];
+  b[0] = x0, b[1] = x1, b[2] = x2;
+}
+
+__device__ void exp_sim3(const float xi[7], float t[3], float q[4], float &s) {
+  // gn_kernels.cu:323-390 (lietorch rxso3 W-matrix coefficients, small-angle/-scale branches)
+  float tau[3] = {xi[0], xi[1], xi[2]};
+  const float phi[3] = {xi[3], xi[4], xi[5]};
+  const float sigma = xi[6];
+  const float scale = expf(sigma);
+  exp_so3(phi, q);
+  s = scale;
+  const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+  const float theta = sqrtf(theta_sq);
+  float A, B, C;
+  const float EPSF = 1e-6f;
+  if (fabsf(sigma) < EPSF) {
+    C = 1.0f;
+    if (fabsf(theta) < EPSF) {
+      A = 0.5f;
+      B = 1.0f / 6.0f;
+    } else {
+      A = (1.0f - cosf(theta)) / theta_sq;
+      B = (theta - sinf(theta)) / (theta_sq * theta);
+    }
+  } else {
+    C = (scale - 1.0f) / sigma;
+    if (fabsf(theta) < EPSF) {
+      const float sigma_sq = sigma * sigma;
+      A = ((sigma - 1.0f) * scale + 1.0f) / sigma_sq;
+      B = (scale * 0.5f * sigma_sq + scale - 1.0f - sigma * scale) / (sigma_sq * sigma);
+    } else {
+      const float a = scale * sinf(theta);
+      const float b = scale * cosf(theta);
+      const float c = theta_sq + sigma * sigma;
+      A = (a * sigma + (1.0f - b) * theta) / (theta * c);
+      B = (C - ((b - 1.0f) * sigma + a * theta) / c) / theta_sq;
+    }
+  }
+  t[0] = C * tau[0], t[1] = C * tau[1], t[2] = C * tau[2];
+  cross_inplace(phi, tau);
+  t[0] += A * tau[0], t[1] += A * tau[1], t[2] += A * tau[2];
+  cross_inplace(phi, tau);
+  t[0] += B * tau[0], t[1] += B * tau[1], t[2] += B * tau[2];
+}
+
+constexpr int kSolveThreads = 512;
+
+__global__ void __launch_bounds__(kSolveThreads)
+    gn_solve_retract_kernel(const double *__restrict__ sys, const double *__restrict__ ldiag,
+                            int D, double *__restrict__ xbuf,
+                            float *__restrict__ Twc, float *__restrict__ dx, int num_poses,
+                            float delta_thresh, int *__restrict__ flags) {
+  if (flags[0]) return;
+  const int t = threadIdx.x;
+  const double *L = sys;
+  const double *rhs = sys + static_cast<size_t>(D) * D;
+  __shared__ double xs[kPB];
+  __shared__ double redn[kSolveThreads / 32];
+  const bool fail = flags[2] != 0;
+
+  if (!fail) {
+    for (int k = t; k < D; k += kSolveThreads) xbuf[k] = rhs[k];
+    __syncthreads();
+    // forward: L y = b, panel by panel
+    for (int k0 = 0; k0 < D; k0 += kPB) {
+      const int pb = min(kPB, D - k0);
+      const double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kPB * kPB;
+      if (t < 32) {  // one warp solves the diagonal block
+        double mine = (t < pb) ? xbuf[k0 + t] : 0.0;
+        for (int c = 0; c < pb; c++) {
+          double yc = 0.0;
+          if (t == c) yc = mine / Ld[c * kPB + c];
+          yc = __shfl_sync(0xffffffffu, yc, c);
+          if (t == c) mine = yc;
+          else if (t > c && t < pb) mine -= Ld[t * kPB + c] * yc;
+        }
+        if (t < pb) {
+          xs[t] = mine;
+          xbuf[k0 + t] = mine;
+        }
+      }
+      __syncthreads();
+      for (int r = k0 + pb + t; r < D; r += kSolveThreads) {
+        double s = xbuf[r];
+        const double *Lr = L + static_cast<size_t>(r) * D + k0;
+        for (int c = 0; c < pb; c++) s -= Lr[c] * xs[c];
+        xbuf[r] = s;
+      }
+      __syncthreads();
+    }
+    // backward: L^T x = y
+    const int last = ((D - 1) / kPB) * kPB;
+    for (int k0 = last; k0 >= 0; k0 -= kPB) {
+      const int pb = min(kPB, D - k0);
+      const double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kPB * kPB;
+      if (t < 32) {
+        double mine = (t < pb) ? xbuf[k0 + t] : 0.0;
+        for (int c = pb - 1; c >= 0; c--) {
+          double xc = 0.0;
+          if (t == c) xc = mine / Ld[c * kPB + c];
+          xc = __shfl_sync(0xffffffffu, xc, c);
+          if (t == c) mine = xc;
+          else if (t < c) mine -= Ld[c * kPB + t] * xc;
+        }
+        if (t < pb) {
+          xs[t] = mine;
+          xbuf[k0 + t] = mine;
+        }
+      }
+      __syncthreads();
+      for (int r = t; r < k0; r += kSolveThreads) {
+        double s = xbuf[r];
+        for (int c = 0; c < pb; c++) s -= L[static_cast<size_t>(k0 + c) * D + r] * xs[c];
+        xbuf[r] = s;
+      }
+      __syncthreads();
+    }
+  }
+
+  // dx = -x (zeros when the factorisation failed or produced non-finite values)
+  __shared__ int nonfinite;
+  if (t == 0) nonfinite = 0;
+  __syncthreads();
+  if (!fail) {
+    int bad = 0;
+    for (int k = t; k < D; k += kSolveThreads)
+      if (!isfinite(xbuf[k])) bad = 1;
+    if (bad) nonfinite = 1;
+  }
+  __syncthreads();
+  const bool zero_step = fail || nonfinite;
+  double nrm = 0.0;
+  for (int k = t; k < D; k += kSolveThreads) {
+    const float d = zero_step ? 0.0f : static_cast<float>(-xbuf[k]);
+    dx[k] = d;
+    nrm += static_cast<double>(d) * static_cast<double>(d);
+  }
+  __syncthreads();
+
+  // left retraction of poses 1..N-1 (pose_retr_kernel :415-453, retrSim3 :392-413)
+  for (int k = 1 + t; k < num_poses; k += kSolveThreads) {
+    float xi[7];
+#pragma unroll
+    for (int m = 0; m < 7; m++) xi[m] = dx[(k - 1) * 7 + m];
+    float *P = Twc + k * 8;
+    const float tt[3] = {P[0], P[1], P[2]};
+    const float q[4] = {P[3], P[4], P[5], P[6]};
+    const float s = P[7];
+    float dt[3], dq[4], ds;
+    exp_sim3(xi, dt, dq, ds);
+    float q1[4], t1[3];
+    quat_mul(dq, q, q1);
+    act_so3<float>(dq, tt, t1);
+    P[0] = t1[0] * ds + dt[0];
+    P[1] = t1[1] * ds + dt[1];
+    P[2] = t1[2] * ds + dt[2];
+    P[3] = q1[0], P[4] = q1[1], P[5] = q1[2], P[6] = q1[3];
+    P[7] = ds * s;
+  }
+
+  // stop test (:1219-1222)
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, off);
+  if ((t & 31) == 0) redn[t >> 5] = nrm;
+  __syncthreads();
+  if (t == 0) {
+    double s = 0.0;
+    for (int k = 0; k < kSolveThreads / 32; k++) s += redn[k];
+    flags[1] += 1;  // iterations executed
+    flags[2] = 0;   // clear the failure flag for the next iteration
+    if (static_cast<float>(sqrt(s)) < delta_thresh) flags[0] = 1;
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// keyframe id -> packed pose index (sorted-unique rank), no host sync
+// ----------------------------------------------------------------------------------------
+__global__ void gn_first_occurrence_kernel(const long long *__restrict__ ii,
+                                           const long long *__restrict__ jj, int E,
+                                           unsigned char *__restrict__ first) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= 2 * E) return;
+  const long long v = (k < E) ? ii[k] : jj[k - E];
+  unsigned char f = 1;
+  for (int m = 0; m < k; m++) {
+    const long long o = (m < E) ? ii[m] : jj[m - E];
+    if (o == v) {
+      f = 0;
+      break;
+    }
+  }
+  first[k] = f;
+}
+
+__global__ void gn_rank_kernel(const long long *__restrict__ ii, const long long *__restrict__ jj,
+                               int E, const unsigned char *__restrict__ first, int num_poses,
+                               int *__restrict__ pose_i, int *__restrict__ pose_j,
+                               int *__restrict__ flags) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k == 0) {
+    flags[0] = 0;  // done
+    flags[1] = 0;  // iterations executed
+    flags[2] = 0;  // factorisation failed
+  }
+  if (k >= 2 * E) return;
+  const long long v = (k < E) ? ii[k] : jj[k - E];
+  int rank = 0;
+  for (int m = 0; m < 2 * E; m++) {
+    const long long o = (m < E) ? ii[m] : jj[m - E];
+    rank += (first[m] && o < v) ? 1 : 0;
+  }
+  rank = min(rank, num_poses - 1);  // memory safety if the caller's N is inconsistent
+  if (k < E) pose_i[k] = rank;
+  else pose_j[k - E] = rank;
+}
+
+}  // namespace m3r
+
+// =========================================================================================
+// host side
+// =========================================================================================
+using namespace m3r;
+
+template <typename T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t cap = 0;
+  // grow-only; contents are not preserved
+  int reserve(size_t want) {
+    if (want <= cap) return M3R_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    const size_t alloc = want + want / 4 + 16;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&p), alloc * sizeof(T));
+    if (e != cudaSuccess) {
+      set_error("cudaMalloc(%zu bytes): %s", alloc * sizeof(T), cudaGetErrorString(e));
+      return M3R_ERR_NO_MEMORY;
+    }
+    cap = alloc;
+    return M3R_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct m3r_gn_workspace {
+  int device = 0;
+  DevBuf<int> pose_i, pose_j;     // [E] packed pose index per directed edge
+  DevBuf<unsigned char> first;    // [2E] scratch of the id remap
+  DevBuf<double> partials;        // [items, 35]
+  DevBuf<double> edge_H, edge_g;  // [E_shard, 49], [E_shard, 7]
+  DevBuf<double> system;          // D*D + D (single-GPU entry points)
+  DevBuf<double> ldiag;           // factored diagonal blocks of the Cholesky
+  DevBuf<double> xbuf;            // [D]
+  int *flags = nullptr;           // [0] done, [1] iterations, [2] factorisation failed
+  int begun_edges = -1;
+};
+
+extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
+  M3R_REQUIRE(out != nullptr, "gn_workspace_create: null out pointer");
+  m3r_gn_workspace *ws = new m3r_gn_workspace();
+  cudaError_t e = cudaGetDevice(&ws->device);
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&ws->flags), 4 * sizeof(int));
+  if (e == cudaSuccess) e = cudaMemset(ws->flags, 0, 4 * sizeof(int));
+  if (e != cudaSuccess) {
+    delete ws;
+    return cuda_fail(e, "gn_workspace_create");
+  }
+  *out = ws;
+  return M3R_OK;
+}
+
+extern "C" void m3r_gn_workspace_destroy(m3r_gn_workspace *ws) {
+  if (!ws) return;
+  ws->pose_i.release(), ws->pose_j.release(), ws->first.release(), ws->partials.release();
+  ws->edge_H.release(), ws->edge_g.release(), ws->system.release(), ws->ldiag.release();
+  ws->xbuf.release();
+  cudaFree(ws->flags);
+  delete ws;
+}
+
+extern "C" int64_t m3r_gn_system_size(int num_poses) {
+  const int64_t D = 7 * static_cast<int64_t>(num_poses > 1 ? num_poses - 1 : 0);
+  return D * D + D;
+}
+
+static int check_problem(const m3r_gn_problem *p) {
+  M3R_REQUIRE(p != nullptr, "gn: null problem");
+  M3R_REQUIRE(p->kind == M3R_GN_RAYS || p->kind == M3R_GN_CALIB || p->kind == M3R_GN_POINTS,
+              "gn: unknown kind %d", p->kind);
+  M3R_REQUIRE(p->num_poses >= 2, "gn: need at least 2 poses (got %d)", p->num_poses);
+  M3R_REQUIRE(p->num_points >= 1 && p->num_edges >= 0, "gn: bad sizes");
+  M3R_REQUIRE(0 <= p->edge_begin && p->edge_begin <= p->edge_end && p->edge_end <= p->num_edges,
+              "gn: bad edge shard [%d,%d) of %d", p->edge_begin, p->edge_end, p->num_edges);
+  M3R_REQUIRE(p->Twc && p->Xs && p->Cs, "gn: null pose/point pointer");
+  M3R_REQUIRE(p->num_edges == 0 || (p->ii && p->jj), "gn: null edge index pointer");
+  M3R_REQUIRE(p->edge_end == p->edge_begin || (p->idx_ii2jj && p->valid_match && p->Q),
+              "gn: null edge data pointer");
+  M3R_REQUIRE(aligned16(p->Twc), "gn: Twc must be 16-byte aligned");
+  if (p->kind == M3R_GN_CALIB) {
+    M3R_REQUIRE(p->K != nullptr, "gn: calib needs K");
+    M3R_REQUIRE(p->width > 0 && p->height > 0, "gn: calib needs image size");
+  }
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, void *stream) {
+  M3R_REQUIRE(ws != nullptr, "gn_begin: null workspace");
+  int rc = check_problem(prob);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int E = prob->num_edges;
+  const size_t want = static_cast<size_t>(E > 0 ? E : 1);
+  if ((rc = ws->pose_i.reserve(want))) return rc;
+  if ((rc = ws->pose_j.reserve(want))) return rc;
+  if ((rc = ws->first.reserve(2 * want))) return rc;
+  ws->begun_edges = E;
+  const int M = 2 * E;
+  const int blocks = (M + 255) / 256;
+  if (blocks > 0) {
+    gn_first_occurrence_kernel<<<blocks, 256, 0, s>>>(
+        reinterpret_cast<const long long *>(prob->ii), reinterpret_cast<const long long *>(prob->jj),
+        E, ws->first.p);
+    M3R_LAUNCH_CHECK("gn_first_occurrence_kernel");
+  }
+  gn_rank_kernel<<<blocks > 0 ? blocks : 1, 256, 0, s>>>(
+      reinterpret_cast<const long long *>(prob->ii), reinterpret_cast<const long long *>(prob->jj), E,
+      ws->first.p, prob->num_poses, ws->pose_i.p, ws->pose_j.p, ws->flags);
+  M3R_LAUNCH_CHECK("gn_rank_kernel");
+  return M3R_OK;
+}
+
+static GnParams make_params(const m3r_gn_problem *p) {
+  GnParams P{};
+  P.C_thresh = p->C_thresh;
+  P.Q_thresh = p->Q_thresh;
+  if (p->kind == M3R_GN_RAYS) {
+    P.sigma_a_inv = 1.0f / p->sigma_ray;
+    P.sigma_b_inv = 1.0f / p->sigma_dist;
+  } else if (p->kind == M3R_GN_CALIB) {
+    P.sigma_a_inv = 1.0f / p->sigma_pixel;
+    P.sigma_b_inv = 1.0f / p->sigma_depth;
+    P.width = p->width;
+    P.height = p->height;
+    // (u > pixel_border) && (u < width - 1 - pixel_border), ints converted to float (:1382-1383)
+    P.u_lo = static_cast<float>(p->pixel_border);
+    P.u_hi = static_cast<float>(p->width - 1 - p->pixel_border);
+    P.v_lo = static_cast<float>(p->pixel_border);
+    P.v_hi = static_cast<float>(p->height - 1 - p->pixel_border);
+    P.z_eps = p->z_eps;
+  } else {
+    P.sigma_a_inv = 1.0f / p->sigma_point;
+  }
+  return P;
+}
+
+template <int KIND>
+static void launch_accumulate(const AccArgs &a, bool vec4, int grid, cudaStream_t s) {
+  if (vec4) gn_accumulate_kernel<KIND, 4><<<grid, kAccThreads, 0, s>>>(a);
+  else gn_accumulate_kernel<KIND, 1><<<grid, kAccThreads, 0, s>>>(a);
+}
+
+extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob, double *system,
+                                void *stream) {
+  M3R_REQUIRE(ws != nullptr && system != nullptr, "gn_linearize: null workspace/system");
+  int rc = check_problem(prob);
+  if (rc) return rc;
+  M3R_REQUIRE(prob->num_edges == ws->begun_edges, "gn_linearize: call m3r_gn_begin first");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int n = prob->num_points;
+  const int ES = prob->edge_end - prob->edge_begin;
+  const int chunks = (n + kChunk - 1) / kChunk;
+  const size_t items = static_cast<size_t>(ES) * chunks;
+  if ((rc = ws->partials.reserve(items * kNAcc + 1))) return rc;
+  if ((rc = ws->edge_H.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 49))) return rc;
+  if ((rc = ws->edge_g.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 7))) return rc;
+
+  if (ES > 0) {
+    AccArgs a{};
+    a.Twc = prob->Twc, a.Xs = prob->Xs, a.Cs = prob->Cs;
+    a.idx = reinterpret_cast<const long long *>(prob->idx_ii2jj);
+    a.valid = prob->valid_match;
+    a.Q = prob->Q;
+    a.pose_i = ws->pose_i.p, a.pose_j = ws->pose_j.p;
+    a.K = prob->K;
+    a.partials = ws->partials.p;
+    a.flags = ws->flags;
+    a.n = n, a.edge_begin = prob->edge_begin, a.num_shard_edges = ES, a.chunks_per_edge = chunks;
+    a.P = make_params(prob);
+    const bool vec4 = (n % 4 == 0) && aligned16(prob->Xs) && aligned16(prob->Cs) &&
+                      aligned16(prob->idx_ii2jj) && aligned16(prob->Q) &&
+                      ((reinterpret_cast<uintptr_t>(prob->valid_match) & 3u) == 0);
+    const size_t cap = static_cast<size_t>(kNumSMs) * 2;
+    const int grid = static_cast<int>(items < cap ? items : cap);
+    if (prob->kind == M3R_GN_RAYS) launch_accumulate<M3R_GN_RAYS>(a, vec4, grid, s);
+    else if (prob->kind == M3R_GN_CALIB) launch_accumulate<M3R_GN_CALIB>(a, vec4, grid, s);
+    else launch_accumulate<M3R_GN_POINTS>(a, vec4, grid, s);
+    M3R_LAUNCH_CHECK("gn_accumulate_kernel");
+
+    gn_edge_finalize_kernel<<<ES, 64, 0, s>>>(ws->partials.p, prob->Twc, ws->pose_i.p,
+                                              prob->edge_begin, chunks, ws->edge_H.p,
+                                              ws->edge_g.p, ws->flags);
+    M3R_LAUNCH_CHECK("gn_edge_finalize_kernel");
+  }
+  const int NB = prob->num_poses - 1;
+  gn_assemble_kernel<<<dim3(NB, NB), 64, 0, s>>>(ws->edge_H.p, ws->edge_g.p, ws->pose_i.p,
+                                                 ws->pose_j.p, prob->edge_begin, ES, NB, system,
+                                                 ws->flags);
+  M3R_LAUNCH_CHECK("gn_assemble_kernel");
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *prob, double *system,
+                                    float *dx, float delta_thresh, void *stream) {
+  M3R_REQUIRE(ws != nullptr && system != nullptr && dx != nullptr, "gn_solve_retract: null pointer");
+  int rc = check_problem(prob);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int D = 7 * (prob->num_poses - 1);
+  if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
+  if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kPB * kPB))) return rc;
+  for (int k0 = 0; k0 < D; k0 += kPB) {
+    const int rows_below = D - k0 - kPB;
+    const int pblocks = rows_below > 0 ? (rows_below + 63) / 64 : 1;
+    chol_panel_kernel<<<pblocks, 64, 0, s>>>(system, ws->ldiag.p, D, k0, ws->flags);
+    M3R_LAUNCH_CHECK("chol_panel_kernel");
+    if (rows_below > 0) {
+      const int tiles = (rows_below + 63) / 64;
+      chol_update_kernel<<<dim3(tiles, tiles), 256, 0, s>>>(system, D, k0, ws->flags);
+      M3R_LAUNCH_CHECK("chol_update_kernel");
+    }
+  }
+  gn_solve_retract_kernel<<<1, kSolveThreads, 0, s>>>(system, ws->ldiag.p, D, ws->xbuf.p,
+                                                      prob->Twc, dx, prob->num_poses,
+                                                      delta_thresh, ws->flags);
+  M3R_LAUNCH_CHECK("gn_solve_retract_kernel");
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_edge_blocks(m3r_gn_workspace *ws, const double **Hjj, const double **gj) {
+  M3R_REQUIRE(ws && Hjj && gj, "gn_edge_blocks: null pointer");
+  *Hjj = ws->edge_H.p;
+  *gj = ws->edge_g.p;
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_iterations_done(m3r_gn_workspace *ws, void *stream, int *iters) {
+  M3R_REQUIRE(ws && iters, "gn_iterations_done: null pointer");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int host[4] = {0, 0, 0, 0};
+  M3R_CUDA_TRY(cudaMemcpyAsync(host, ws->flags, sizeof(host), cudaMemcpyDeviceToHost, s));
+  M3R_CUDA_TRY(cudaStreamSynchronize(s));
+  *iters = host[1];
+  return M3R_OK;
+}
+
+static int run_gn(m3r_gn_workspace *ws, m3r_gn_problem *p, float *dx, int max_iter,
+                  float delta_thresh, void *stream) {
+  M3R_REQUIRE(ws != nullptr, "gauss_newton: null workspace");
+  M3R_REQUIRE(dx != nullptr, "gauss_newton: null dx");
+  p->edge_begin = 0;
+  p->edge_end = p->num_edges;
+  int rc = m3r_gn_begin(ws, p, stream);
+  if (rc) return rc;
+  const size_t need = static_cast<size_t>(m3r_gn_system_size(p->num_poses));
+  if ((rc = ws->system.reserve(need))) return rc;
+  for (int it = 0; it < max_iter; it++) {
+    if ((rc = m3r_gn_linearize(ws, p, ws->system.p, stream))) return rc;
+    if ((rc = m3r_gn_solve_retract(ws, p, ws->system.p, dx, delta_thresh, stream))) return rc;
+  }
+  return M3R_OK;
+}
+
+extern "C" int m3r_gauss_newton_rays(m3r_gn_workspace *ws, float *Twc, const float *Xs,
+                                     const float *Cs, const int64_t *ii, const int64_t *jj,
+                                     const int64_t *idx_ii2jj, const uint8_t *valid_match,
+                                     const float *Q, float *dx, int num_poses, int num_points,
+                                     int num_edges, float sigma_ray, float sigma_dist,
+                                     float C_thresh, float Q_thresh, int max_iter,
+                                     float delta_thresh, void *stream) {
+  m3r_gn_problem p{};
+  p.kind = M3R_GN_RAYS;
+  p.num_poses = num_poses, p.num_points = num_points, p.num_edges = num_edges;
+  p.Twc = Twc, p.Xs = Xs, p.Cs = Cs, p.ii = ii, p.jj = jj;
+  p.idx_ii2jj = idx_ii2jj, p.valid_match = valid_match, p.Q = Q;
+  p.sigma_ray = sigma_ray, p.sigma_dist = sigma_dist;
+  p.C_thresh = C_thresh, p.Q_thresh = Q_thresh;
+  return run_gn(ws, &p, dx, max_iter, delta_thresh, stream);
+}
+
+extern "C" int m3r_gauss_newton_calib(m3r_gn_workspace *ws, float *Twc, const float *Xs,
+                                      const float *Cs, const float *K, const int64_t *ii,
+                                      const int64_t *jj, const int64_t *idx_ii2jj,
+                                      const uint8_t *valid_match, const float *Q, float *dx,
+                                      int num_poses, int num_points, int num_edges, int height,
+                                      int width, int pixel_border, float z_eps, float sigma_pixel,
+                                      float sigma_depth, float C_thresh, float Q_thresh,
+                                      int max_iter, float delta_thresh, void *stream) {
+  m3r_gn_problem p{};
+  p.kind = M3R_GN_CALIB;
+  p.num_poses = num_poses, p.num_points = num_points, p.num_edges = num_edges;
+  p.Twc = Twc, p.Xs = Xs, p.Cs = Cs, p.ii = ii, p.jj = jj;
+  p.idx_ii2jj = idx_ii2jj, p.valid_match = valid_match, p.Q = Q;
+  p.K = K, p.height = height, p.width = width, p.pixel_border = pixel_border;
+  p.z_eps = z_eps, p.sigma_pixel = sigma_pixel, p.sigma_depth = sigma_depth;
+  p.C_thresh = C_thresh, p.Q_thresh = Q_thresh;
+  return run_gn(ws, &p, dx, max_iter, delta_thresh, stream);
+}
+
+extern "C" int m3r_gauss_newton_points(m3r_gn_workspace *ws, float *Twc, const float *Xs,
+                                       const float *Cs, const int64_t *ii, const int64_t *jj,
+                                       const int64_t *idx_ii2jj, const uint8_t *valid_match,
+                                       const float *Q, float *dx, int num_poses, int num_points,
+                                       int num_edges, float sigma_point, float C_thresh,
+                                       float Q_thresh, int max_iter, float delta_thresh,
+                                       void *stream) {
+  m3r_gn_problem p{};
+  p.kind = M3R_GN_POINTS;
+  p.num_poses = num_poses, p.num_points = num_points, p.num_edges = num_edges;
+  p.Twc = Twc, p.Xs = Xs, p.Cs = Cs, p.ii = ii, p.jj = jj;
+  p.idx_ii2jj = idx_ii2jj, p.valid_match = valid_match, p.Q = Q;
+  p.sigma_point = sigma_point;
+  p.C_thresh = C_thresh, p.Q_thresh = Q_thresh;
+  return run_gn(ws, &p, dx, max_iter, delta_thresh, stream);
+}

@@ -1,0 +1,535 @@
+// Iterative projective matching and descriptor refinement for sm_100a.
+//
+// Replaces the reference's matching_kernels.cu (iter_proj_kernel :119-275,
+// refine_matches_kernel :25-81) behind the C ABI of include/m3r_backends.h.  Written from
+// the behaviour of those kernels, not from their code: one warp handles 32 neighbouring
+// query points and stages the ray-image texels they touch through shared memory; the
+// descriptor search runs two candidates per half2 lane with per-operation rounding.
+#include <cuda_fp16.h>
+
+#include "m3r_common.cuh"
+
+namespace m3r {
+
+// =========================================================================================
+// iter_proj
+// =========================================================================================
+//
+// Arithmetic contract (what makes the integer match indices agree with the reference):
+//  * bilinear weights: the reference evaluates (1.0-du)*dv etc. in double and rounds to
+//    float (matching_kernels.cu:162-164).  du = u - floor(u) with u >= 1 is a multiple of
+//    2^-23, so 1-du is exact in float and the float product rounds the same exact value
+//    once: identical bits, no double needed.
+//  * 1.0/r_norm and 1.0/det (:187,:213,:246): double division rounded to float equals the
+//    correctly rounded float reciprocal (double rounding is innocuous for p=24 -> p=53),
+//    i.e. __frcp_rn.
+//  * lambda *= 0.1 (:262) is a double multiply by the double 0.1: reproduced in double.
+//    lambda *= 10.0 (:266) is exact in double, hence equal to the float multiply.
+//  * sqrtf is IEEE (default -prec-sqrt=true), fmin/fmax clamp as :21-23.
+//  * multiply-add chains are written in the reference's association order so that nvcc's
+//    FMA contraction produces the same instruction pattern.
+
+struct Texel9 {
+  float c[9];
+};
+
+__device__ __forceinline__ float clampf(float x, float lo, float hi) {
+  return fminf(fmaxf(x, lo), hi);
+}
+
+// One LM evaluation at (u,v): interpolated ray (normalised), gradients, cost.
+template <bool kWithGrad, typename Fetch>
+__device__ __forceinline__ void eval_at(Fetch fetch, float u, float v, const float pt[3],
+                                        float gx[3], float gy[3], float err[3], float &cost) {
+  const int u11 = static_cast<int>(floorf(u));
+  const int v11 = static_cast<int>(floorf(v));
+  const float du = u - static_cast<float>(u11);
+  const float dv = v - static_cast<float>(v11);
+  const float w11 = du * dv;
+  const float w12 = (1.0f - du) * dv;
+  const float w21 = du * (1.0f - dv);
+  const float w22 = (1.0f - du) * (1.0f - dv);
+  constexpr int NC = kWithGrad ? 9 : 3;
+  float r11[NC], r12[NC], r21[NC], r22[NC];
+  fetch(u11 + 1, v11 + 1, r11);  // weighted by w11 (:167)
+  fetch(u11, v11 + 1, r12);
+  fetch(u11 + 1, v11, r21);
+  fetch(u11, v11, r22);
+  float r[3];
+#pragma unroll
+  for (int j = 0; j < 3; j++) r[j] = w11 * r11[j] + w12 * r12[j] + w21 * r21[j] + w22 * r22[j];
+  if (kWithGrad) {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      gx[j] = w11 * r11[3 + j] + w12 * r12[3 + j] + w21 * r21[3 + j] + w22 * r22[3 + j];
+      gy[j] = w11 * r11[6 + j] + w12 * r12[6 + j] + w21 * r21[6 + j] + w22 * r22[6 + j];
+    }
+  }
+  const float r_norm = sqrtf(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+  const float r_norm_inv = __frcp_rn(r_norm);
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    r[j] *= r_norm_inv;
+    err[j] = r[j] - pt[j];
+  }
+  cost = err[0] * err[0] + err[1] * err[1] + err[2] * err[2];
+}
+
+// Per-warp staging of the texels a gather touches.  The 32 lanes of a warp hold
+// neighbouring query points, whose 2x2 bilinear footprints overlap and sit on at most a few
+// image rows while the match field is smooth.  The warp copies the bounding box of all
+// footprints from global (coalesced, every 128-byte line once) into its shared-memory tile
+// and the lanes then read their corners from there: with the [h,w,9] layout the API fixes
+// (36-byte texels, only 4-byte aligned) a direct per-lane gather touches ~9 lines per load
+// instruction, the staged copy ~1.3.  If the box does not fit the tile (arbitrary p_init),
+// the warp falls back to direct global loads for that gather: same values either way.
+constexpr int kIpWarps = 4;             // warps per CTA
+constexpr int kIpTileFloats = 1728;     // per-warp tile: 192 texels * 9 floats = 6912 B
+
+struct WarpTile {
+  float *smem;   // this warp's tile
+  int umin, vmin, wt, ht;
+  bool staged;
+};
+
+template <int NCH>  // channels needed per texel: 9 (ray+grads) or 3 (ray only)
+__device__ __forceinline__ WarpTile stage_tile(const float *__restrict__ img, int w, float *tile,
+                                               int u11, int v11, int lane) {
+  WarpTile t;
+  t.smem = tile;
+  const int umin = __reduce_min_sync(0xffffffffu, u11);
+  const int umax = __reduce_max_sync(0xffffffffu, u11) + 1;
+  const int vmin = __reduce_min_sync(0xffffffffu, v11);
+  const int vmax = __reduce_max_sync(0xffffffffu, v11) + 1;
+  t.umin = umin;
+  t.vmin = vmin;
+  t.wt = umax - umin + 1;
+  t.ht = vmax - vmin + 1;
+  t.staged = (t.wt * t.ht * 9 <= kIpTileFloats);
+  if (t.staged) {
+    __syncwarp();  // previous readers of the tile are done
+    const int row_floats = t.wt * 9;
+    for (int rrow = 0; rrow < t.ht; rrow++) {
+      const float *src = img + (static_cast<size_t>(vmin + rrow) * w + umin) * 9;
+      float *dst = tile + rrow * row_floats;
+      if (NCH == 9) {
+        for (int k = lane; k < row_floats; k += 32) dst[k] = __ldg(src + k);
+      } else {
+        // only channels 0..2 of each texel
+        for (int k = lane; k < t.wt * 3; k += 32) {
+          const int tx = k / 3, ch = k - tx * 3;
+          dst[tx * 9 + ch] = __ldg(src + tx * 9 + ch);
+        }
+      }
+    }
+    __syncwarp();
+  }
+  return t;
+}
+
+template <bool kStaged>
+__global__ void __launch_bounds__(kIpWarps * 32)
+    iter_proj_kernel(const float *__restrict__ rays, const float *__restrict__ pts,
+                     const float *__restrict__ p_init, float *__restrict__ p_new,
+                     uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,
+                     float lambda_init, float cost_thresh) {
+  __shared__ float tiles[kStaged ? kIpWarps * kIpTileFloats : 1];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = idx < n;
+  if (!active) idx = n - 1;  // inactive lanes shadow the last point (keeps warps whole)
+  const size_t gi = static_cast<size_t>(b) * n + idx;
+  const float *img = rays + static_cast<size_t>(b) * h * w * 9;
+  float *tile = tiles + (kStaged ? warp * kIpTileFloats : 0);
+
+  float u = __ldg(p_init + gi * 2 + 0);
+  float v = __ldg(p_init + gi * 2 + 1);
+  const float pt[3] = {__ldg(pts + gi * 3 + 0), __ldg(pts + gi * 3 + 1), __ldg(pts + gi * 3 + 2)};
+  u = clampf(u, 1.0f, static_cast<float>(w - 2));
+  v = clampf(v, 1.0f, static_cast<float>(h - 2));
+
+  float lambda = lambda_init;
+  bool conv = false;
+  for (int it = 0; it < max_iter; it++) {
+    float gx[3], gy[3], err[3], cost;
+    if (kStaged) {
+      const WarpTile t = stage_tile<9>(img, w, tile, static_cast<int>(floorf(u)),
+                                       static_cast<int>(floorf(v)), lane);
+      if (t.staged) {
+        auto fetch = [&](int uu, int vv, float *out) {
+          const float *s = t.smem + ((vv - t.vmin) * t.wt + (uu - t.umin)) * 9;
+#pragma unroll
+          for (int c = 0; c < 9; c++) out[c] = s[c];
+        };
+        eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
+      } else {
+        auto fetch = [&](int uu, int vv, float *out) {
+          const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
+#pragma unroll
+          for (int c = 0; c < 9; c++) out[c] = __ldg(s + c);
+        };
+        eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
+      }
+    } else {
+      auto fetch = [&](int uu, int vv, float *out) {
+        const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
+#pragma unroll
+        for (int c = 0; c < 9; c++) out[c] = __ldg(s + c);
+      };
+      eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
+    }
+
+    // 2x2 normal equations with the LM diagonal (:202-215)
+    float A00 = gx[0] * gx[0] + gx[1] * gx[1] + gx[2] * gx[2];
+    const float A01 = gx[0] * gy[0] + gx[1] * gy[1] + gx[2] * gy[2];
+    float A11 = gy[0] * gy[0] + gy[1] * gy[1] + gy[2] * gy[2];
+    const float b0 = -(err[0] * gx[0] + err[1] * gx[1] + err[2] * gx[2]);
+    const float b1 = -(err[0] * gy[0] + err[1] * gy[1] + err[2] * gy[2]);
+    A00 += lambda;
+    A11 += lambda;
+    const float det_inv = __frcp_rn(A00 * A11 - A01 * A01);
+    const float delta_u = det_inv * (A11 * b0 - A01 * b1);
+    const float delta_v = det_inv * (-A01 * b0 + A00 * b1);
+    const float u_new = clampf(u + delta_u, 1.0f, static_cast<float>(w - 2));
+    const float v_new = clampf(v + delta_v, 1.0f, static_cast<float>(h - 2));
+
+    // cost at the trial pixel, ray channels only (:225-256)
+    float err2[3], new_cost;
+    if (kStaged) {
+      const WarpTile t = stage_tile<3>(img, w, tile, static_cast<int>(floorf(u_new)),
+                                       static_cast<int>(floorf(v_new)), lane);
+      if (t.staged) {
+        auto fetch = [&](int uu, int vv, float *out) {
+          const float *s = t.smem + ((vv - t.vmin) * t.wt + (uu - t.umin)) * 9;
+#pragma unroll
+          for (int c = 0; c < 3; c++) out[c] = s[c];
+        };
+        eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+      } else {
+        auto fetch = [&](int uu, int vv, float *out) {
+          const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
+#pragma unroll
+          for (int c = 0; c < 3; c++) out[c] = __ldg(s + c);
+        };
+        eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+      }
+    } else {
+      auto fetch = [&](int uu, int vv, float *out) {
+        const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
+#pragma unroll
+        for (int c = 0; c < 3; c++) out[c] = __ldg(s + c);
+      };
+      eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+    }
+
+    if (new_cost < cost) {  // accept (:259-264)
+      u = u_new;
+      v = v_new;
+      lambda = static_cast<float>(static_cast<double>(lambda) * 0.1);
+      conv = new_cost < cost_thresh;
+    } else {  // reject (:265-268)
+      lambda = lambda * 10.0f;
+      conv = cost < cost_thresh;
+    }
+  }
+
+  if (active) {
+    reinterpret_cast<float2 *>(p_new)[gi] = make_float2(u, v);
+    converged[gi] = conv ? 1 : 0;
+  }
+}
+
+// =========================================================================================
+// refine_matches
+// =========================================================================================
+//
+// Bit-exactness contract: the reference accumulates `score += D21[k]*D11[k]` in the tensor
+// dtype (matching_kernels.cu:60-63).  For c10::Half both the product and the sum are formed
+// in float and rounded to binary16 (torch/headeronly/util/Half.h operator*, operator+);
+// since float carries 24 >= 2*11+2 bits that equals one correctly rounded half multiply
+// followed by one correctly rounded half add: __hmul2_rn / __hadd2_rn (the _rn forms also
+// forbid ptxas from fusing them into HFMA2, which rounds once and would differ).  The k loop
+// is sequential, so the two half2 lanes carry two different CANDIDATES, never two k's.
+// Ties and the starting score follow :47-69: candidates are visited i-outer/j-inner, a
+// candidate wins only with a strictly greater score, and max_score starts at
+// numeric_limits<c10::Half>::min(), which libcu++ leaves unspecialised, i.e. Half() = +0.
+
+constexpr int kRefineThreads = 128;
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  return __byte_perm(a, b, sel);
+}
+__device__ __forceinline__ __half2 as_h2(uint32_t x) { return *reinterpret_cast<__half2 *>(&x); }
+
+template <int FDIM>  // multiple of 8 (uint4 rows)
+__global__ void __launch_bounds__(kRefineThreads)
+    refine_f16_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
+                      const long long *__restrict__ p1, long long *__restrict__ p1_new, int h,
+                      int w, int n, int radius, int dilation_max) {
+  constexpr int NW = FDIM / 2;  // 32-bit words per descriptor row
+  constexpr int NV = FDIM / 8;  // uint4 per row
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const int b = blockIdx.y;
+  const size_t gi = static_cast<size_t>(b) * n + idx;
+
+  const longlong2 p = reinterpret_cast<const longlong2 *>(p1)[gi];
+  // Candidates further than radius*dilation_max from the image can never be inside it.
+  const long long reach = static_cast<long long>(radius) * dilation_max;
+  if (p.x < -reach || p.x >= w + reach || p.y < -reach || p.y >= h + reach) {
+    reinterpret_cast<longlong2 *>(p1_new)[gi] = p;
+    return;
+  }
+  int u0 = static_cast<int>(p.x), v0 = static_cast<int>(p.y);
+  int u_new = u0, v_new = v0;
+
+  // query descriptor, kept in registers with each element broadcast to both half2 lanes
+  uint32_t qlo[NW], qhi[NW];
+  {
+    const uint4 *qrow = reinterpret_cast<const uint4 *>(D21 + gi * FDIM);
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+      const uint4 t = __ldg(qrow + i);
+      const uint32_t wds[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        qlo[i * 4 + j] = prmt(wds[j], wds[j], 0x1010);
+        qhi[i * 4 + j] = prmt(wds[j], wds[j], 0x3232);
+      }
+    }
+  }
+  const uint4 *img = reinterpret_cast<const uint4 *>(D11 + static_cast<size_t>(b) * h * w * FDIM);
+
+  __half max_score = __ushort_as_half(0);  // +0
+  const int nside = 2 * radius + 1;
+  const int ncand = nside * nside;
+
+  for (int d = dilation_max; d > 0; d--) {
+    const int rd = radius * d;
+    for (int c = 0; c < ncand; c += 2) {
+      // candidate pair (c, c+1) in the reference's scan order: i outer (u), j inner (v)
+      const int ia = c / nside, ja = c - ia * nside;
+      int ib = ia, jb = ja + 1;
+      if (jb == nside) {
+        jb = 0;
+        ib = ia + 1;
+      }
+      const int ua = u0 - rd + ia * d, va = v0 - rd + ja * d;
+      const int ub = u0 - rd + ib * d, vb = v0 - rd + jb * d;
+      const bool ina = (va >= 0) & (va < h) & (ua >= 0) & (ua < w);
+      const bool inb = (c + 1 < ncand) & (vb >= 0) & (vb < h) & (ub >= 0) & (ub < w);
+      if (!(ina | inb)) continue;
+      // out-of-image lanes read a clamped (valid) row and are masked afterwards
+      const int uac = min(max(ua, 0), w - 1), vac = min(max(va, 0), h - 1);
+      const int ubc = min(max(ub, 0), w - 1), vbc = min(max(vb, 0), h - 1);
+      const uint4 *ra = img + (static_cast<size_t>(vac) * w + uac) * NV;
+      const uint4 *rb = img + (static_cast<size_t>(vbc) * w + ubc) * NV;
+      uint32_t wa[NW], wb[NW];
+#pragma unroll
+      for (int i = 0; i < NV; i++) {
+        const uint4 ta = __ldg(ra + i);
+        const uint4 tb = __ldg(rb + i);
+        wa[i * 4 + 0] = ta.x, wa[i * 4 + 1] = ta.y, wa[i * 4 + 2] = ta.z, wa[i * 4 + 3] = ta.w;
+        wb[i * 4 + 0] = tb.x, wb[i * 4 + 1] = tb.y, wb[i * 4 + 2] = tb.z, wb[i * 4 + 3] = tb.w;
+      }
+      __half2 acc = as_h2(0u);
+#pragma unroll
+      for (int m = 0; m < NW; m++) {
+        const __half2 even = as_h2(prmt(wa[m], wb[m], 0x5410));  // (a[2m],   b[2m])
+        const __half2 odd = as_h2(prmt(wa[m], wb[m], 0x7632));   // (a[2m+1], b[2m+1])
+        acc = __hadd2_rn(acc, __hmul2_rn(as_h2(qlo[m]), even));
+        acc = __hadd2_rn(acc, __hmul2_rn(as_h2(qhi[m]), odd));
+      }
+      const __half sa = __low2half(acc), sb = __high2half(acc);
+      if (ina && __hgt(sa, max_score)) {
+        max_score = sa;
+        u_new = ua;
+        v_new = va;
+      }
+      if (inb && __hgt(sb, max_score)) {
+        max_score = sb;
+        u_new = ub;
+        v_new = vb;
+      }
+    }
+    u0 = u_new;  // recentre for the next dilation level (:75-76)
+    v0 = v_new;
+  }
+  reinterpret_cast<longlong2 *>(p1_new)[gi] =
+      make_longlong2(static_cast<long long>(u_new), static_cast<long long>(v_new));
+}
+
+// Generic path: any fdim, any of the three dtypes; accumulation in T as the reference does.
+template <typename T>
+struct RefineOps;
+template <>
+struct RefineOps<__half> {
+  using acc_t = __half;
+  static __device__ __forceinline__ acc_t zero() { return __ushort_as_half(0); }
+  static __device__ __forceinline__ acc_t init_max() { return __ushort_as_half(0); }
+  static __device__ __forceinline__ acc_t mac(acc_t s, __half a, __half b) {
+    return __hadd_rn(s, __hmul_rn(a, b));
+  }
+  static __device__ __forceinline__ bool gt(acc_t a, acc_t b) { return __hgt(a, b); }
+};
+template <>
+struct RefineOps<float> {
+  using acc_t = float;
+  static __device__ __forceinline__ acc_t zero() { return 0.0f; }
+  static __device__ __forceinline__ acc_t init_max() { return 1.17549435e-38f; }  // FLT_MIN
+  static __device__ __forceinline__ acc_t mac(acc_t s, float a, float b) {
+    s += a * b;  // contracted to FFMA by nvcc exactly as in the reference build
+    return s;
+  }
+  static __device__ __forceinline__ bool gt(acc_t a, acc_t b) { return a > b; }
+};
+template <>
+struct RefineOps<double> {
+  using acc_t = double;
+  static __device__ __forceinline__ acc_t zero() { return 0.0; }
+  static __device__ __forceinline__ acc_t init_max() { return 2.2250738585072014e-308; }
+  static __device__ __forceinline__ acc_t mac(acc_t s, double a, double b) {
+    s += a * b;
+    return s;
+  }
+  static __device__ __forceinline__ bool gt(acc_t a, acc_t b) { return a > b; }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kRefineThreads)
+    refine_generic_kernel(const T *__restrict__ D11, const T *__restrict__ D21,
+                          const long long *__restrict__ p1, long long *__restrict__ p1_new,
+                          int h, int w, int n, int fdim, int radius, int dilation_max) {
+  using Ops = RefineOps<T>;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const int b = blockIdx.y;
+  const size_t gi = static_cast<size_t>(b) * n + idx;
+  long long u0 = p1[gi * 2 + 0], v0 = p1[gi * 2 + 1];
+  long long u_new = u0, v_new = v0;
+  const T *q = D21 + gi * fdim;
+  const T *img = D11 + static_cast<size_t>(b) * h * w * fdim;
+  typename Ops::acc_t max_score = Ops::init_max();
+  for (int d = dilation_max; d > 0; d--) {
+    const int rd = radius * d;
+    const int diam = 2 * rd + 1;
+    for (int i = 0; i < diam; i += d) {
+      for (int j = 0; j < diam; j += d) {
+        const long long u = u0 - rd + i;
+        const long long v = v0 - rd + j;
+        if (v >= 0 && v < h && u >= 0 && u < w) {
+          const T *row = img + (static_cast<size_t>(v) * w + static_cast<size_t>(u)) * fdim;
+          typename Ops::acc_t score = Ops::zero();
+          for (int k = 0; k < fdim; k++) score = Ops::mac(score, q[k], row[k]);
+          if (Ops::gt(score, max_score)) {
+            max_score = score;
+            u_new = u;
+            v_new = v;
+          }
+        }
+      }
+    }
+    u0 = u_new;
+    v0 = v_new;
+  }
+  p1_new[gi * 2 + 0] = u_new;
+  p1_new[gi * 2 + 1] = v_new;
+}
+
+}  // namespace m3r
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+using namespace m3r;
+
+extern "C" int m3r_iter_proj_v(const float *rays, const float *pts, const float *p_init,
+                               float *p_new, uint8_t *converged, int b, int h, int w, int n,
+                               int max_iter, float lambda_init, float cost_thresh, int variant,
+                               void *stream) {
+  M3R_REQUIRE(b >= 0 && n >= 0, "iter_proj: negative batch or point count");
+  if (b == 0 || n == 0) return M3R_OK;
+  M3R_REQUIRE(rays && pts && p_init && p_new && converged, "iter_proj: null pointer");
+  M3R_REQUIRE(h >= 3 && w >= 3, "iter_proj: image must be at least 3x3 (got %dx%d)", h, w);
+  M3R_REQUIRE(b <= 65535, "iter_proj: batch %d exceeds grid.y limit", b);
+  M3R_REQUIRE((reinterpret_cast<uintptr_t>(p_new) & 7u) == 0, "iter_proj: p_new not 8-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const dim3 block(kIpWarps * 32);
+  const dim3 grid((n + block.x - 1) / block.x, b);
+  if (variant == 1) {
+    iter_proj_kernel<false><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
+                                                   max_iter, lambda_init, cost_thresh);
+  } else if (variant == 0 || variant == 2) {
+    iter_proj_kernel<true><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
+                                                  max_iter, lambda_init, cost_thresh);
+  } else {
+    set_error("iter_proj: unknown variant %d", variant);
+    return M3R_ERR_INVALID_ARGUMENT;
+  }
+  M3R_LAUNCH_CHECK("iter_proj_kernel");
+  return M3R_OK;
+}
+
+extern "C" int m3r_iter_proj(const float *rays, const float *pts, const float *p_init,
+                             float *p_new, uint8_t *converged, int b, int h, int w, int n,
+                             int max_iter, float lambda_init, float cost_thresh, void *stream) {
+  return m3r_iter_proj_v(rays, pts, p_init, p_new, converged, b, h, w, n, max_iter, lambda_init,
+                         cost_thresh, 0, stream);
+}
+
+extern "C" int m3r_refine_matches_v(const void *D11, const void *D21, const int64_t *p1,
+                                    int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                    int dtype, int radius, int dilation_max, int variant,
+                                    void *stream) {
+  M3R_REQUIRE(b >= 0 && n >= 0, "refine_matches: negative batch or point count");
+  if (b == 0 || n == 0) return M3R_OK;
+  M3R_REQUIRE(D11 && D21 && p1 && p1_new, "refine_matches: null pointer");
+  M3R_REQUIRE(h > 0 && w > 0 && fdim >= 0, "refine_matches: bad shape");
+  M3R_REQUIRE(b <= 65535, "refine_matches: batch %d exceeds grid.y limit", b);
+  M3R_REQUIRE(radius >= 0 && radius <= 1024 && dilation_max <= 1024,
+              "refine_matches: radius/dilation out of range");
+  M3R_REQUIRE((reinterpret_cast<uintptr_t>(p1) & 15u) == 0 &&
+                  (reinterpret_cast<uintptr_t>(p1_new) & 15u) == 0,
+              "refine_matches: p1/p1_new must be 16-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const dim3 block(kRefineThreads);
+  const dim3 grid((n + block.x - 1) / block.x, b);
+  const long long *p1l = reinterpret_cast<const long long *>(p1);
+  long long *p1nl = reinterpret_cast<long long *>(p1_new);
+  if (dtype == M3R_DTYPE_F16) {
+    const bool fast = (fdim == 24) && aligned16(D11) && aligned16(D21) && variant != 1;
+    if (fast) {
+      refine_f16_kernel<24><<<grid, block, 0, s>>>(static_cast<const __half *>(D11),
+                                                   static_cast<const __half *>(D21), p1l, p1nl,
+                                                   h, w, n, radius, dilation_max);
+    } else {
+      refine_generic_kernel<__half><<<grid, block, 0, s>>>(
+          static_cast<const __half *>(D11), static_cast<const __half *>(D21), p1l, p1nl, h, w, n,
+          fdim, radius, dilation_max);
+    }
+  } else if (dtype == M3R_DTYPE_F32) {
+    refine_generic_kernel<float><<<grid, block, 0, s>>>(static_cast<const float *>(D11),
+                                                        static_cast<const float *>(D21), p1l,
+                                                        p1nl, h, w, n, fdim, radius,
+                                                        dilation_max);
+  } else if (dtype == M3R_DTYPE_F64) {
+    refine_generic_kernel<double><<<grid, block, 0, s>>>(static_cast<const double *>(D11),
+                                                         static_cast<const double *>(D21), p1l,
+                                                         p1nl, h, w, n, fdim, radius,
+                                                         dilation_max);
+  } else {
+    set_error("refine_matches: unknown dtype code %d", dtype);
+    return M3R_ERR_INVALID_ARGUMENT;
+  }
+  M3R_LAUNCH_CHECK("refine_matches_kernel");
+  return M3R_OK;
+}
+
+extern "C" int m3r_refine_matches(const void *D11, const void *D21, const int64_t *p1,
+                                  int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                  int dtype, int radius, int dilation_max, void *stream) {
+  return m3r_refine_matches_v(D11, D21, p1, p1_new, b, h, w, n, fdim, dtype, radius,
+                              dilation_max, 0, stream);
+}

@@ -1,0 +1,152 @@
+"""ctypes binding of libm3r_b200.so (the C ABI declared in include/m3r_backends.h).
+
+There is no CPU fallback: if the CUDA library is missing the import fails loudly.
+Build it with `python __graft_entry__.py build` (or `python lightweight-mast3r-slam_b200/build.py`).
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.environ.get(
+    "M3R_B200_LIB", os.path.join(os.path.dirname(_HERE), "libm3r_b200.so")
+)
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"mast3r_slam_backends: CUDA library {LIB_PATH} not found. There is no CPU fallback; "
+        "build it with `python __graft_entry__.py build`."
+    )
+
+lib = ctypes.CDLL(LIB_PATH)
+
+c_int, c_float, c_void_p, c_int64 = ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_int64
+
+M3R_OK = 0
+DTYPE_F16, DTYPE_F32, DTYPE_F64 = 0, 1, 2
+GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
+
+
+class GnProblem(ctypes.Structure):
+    """Mirror of `m3r_gn_problem` (include/m3r_backends.h)."""
+
+    _fields_ = [
+        ("kind", c_int),
+        ("num_poses", c_int),
+        ("num_points", c_int),
+        ("num_edges", c_int),
+        ("edge_begin", c_int),
+        ("edge_end", c_int),
+        ("Twc", c_void_p),
+        ("Xs", c_void_p),
+        ("Cs", c_void_p),
+        ("ii", c_void_p),
+        ("jj", c_void_p),
+        ("idx_ii2jj", c_void_p),
+        ("valid_match", c_void_p),
+        ("Q", c_void_p),
+        ("sigma_ray", c_float),
+        ("sigma_dist", c_float),
+        ("K", c_void_p),
+        ("height", c_int),
+        ("width", c_int),
+        ("pixel_border", c_int),
+        ("z_eps", c_float),
+        ("sigma_pixel", c_float),
+        ("sigma_depth", c_float),
+        ("sigma_point", c_float),
+        ("C_thresh", c_float),
+        ("Q_thresh", c_float),
+    ]
+
+
+def _sig(name, restype, argtypes):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = argtypes
+    return fn
+
+
+abi_version = _sig("m3r_abi_version", c_int, [])
+last_error = _sig("m3r_last_error", ctypes.c_char_p, [])
+launch_count = _sig("m3r_launch_count", ctypes.c_uint64, [])
+
+iter_proj = _sig(
+    "m3r_iter_proj",
+    c_int,
+    [c_void_p] * 5 + [c_int] * 5 + [c_float, c_float, c_void_p],
+)
+iter_proj_v = _sig(
+    "m3r_iter_proj_v",
+    c_int,
+    [c_void_p] * 5 + [c_int] * 5 + [c_float, c_float, c_int, c_void_p],
+)
+refine_matches = _sig(
+    "m3r_refine_matches", c_int, [c_void_p] * 4 + [c_int] * 8 + [c_void_p]
+)
+refine_matches_v = _sig(
+    "m3r_refine_matches_v", c_int, [c_void_p] * 4 + [c_int] * 9 + [c_void_p]
+)
+
+gn_workspace_create = _sig("m3r_gn_workspace_create", c_int, [ctypes.POINTER(c_void_p)])
+gn_workspace_destroy = _sig("m3r_gn_workspace_destroy", None, [c_void_p])
+
+gauss_newton_rays = _sig(
+    "m3r_gauss_newton_rays",
+    c_int,
+    [c_void_p] * 10 + [c_int] * 3 + [c_float] * 4 + [c_int, c_float, c_void_p],
+)
+gauss_newton_calib = _sig(
+    "m3r_gauss_newton_calib",
+    c_int,
+    [c_void_p] * 11 + [c_int] * 6 + [c_float] * 5 + [c_int, c_float, c_void_p],
+)
+gauss_newton_points = _sig(
+    "m3r_gauss_newton_points",
+    c_int,
+    [c_void_p] * 10 + [c_int] * 3 + [c_float] * 3 + [c_int, c_float, c_void_p],
+)
+
+gn_system_size = _sig("m3r_gn_system_size", c_int64, [c_int])
+gn_begin = _sig("m3r_gn_begin", c_int, [c_void_p, ctypes.POINTER(GnProblem), c_void_p])
+gn_linearize = _sig(
+    "m3r_gn_linearize", c_int, [c_void_p, ctypes.POINTER(GnProblem), c_void_p, c_void_p]
+)
+gn_solve_retract = _sig(
+    "m3r_gn_solve_retract",
+    c_int,
+    [c_void_p, ctypes.POINTER(GnProblem), c_void_p, c_void_p, c_float, c_void_p],
+)
+gn_edge_blocks = _sig(
+    "m3r_gn_edge_blocks", c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p)]
+)
+gn_iterations_done = _sig(
+    "m3r_gn_iterations_done", c_int, [c_void_p, c_void_p, ctypes.POINTER(c_int)]
+)
+
+# every symbol include/m3r_backends.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "m3r_abi_version",
+    "m3r_last_error",
+    "m3r_launch_count",
+    "m3r_iter_proj",
+    "m3r_iter_proj_v",
+    "m3r_refine_matches",
+    "m3r_refine_matches_v",
+    "m3r_gn_workspace_create",
+    "m3r_gn_workspace_destroy",
+    "m3r_gauss_newton_rays",
+    "m3r_gauss_newton_calib",
+    "m3r_gauss_newton_points",
+    "m3r_gn_system_size",
+    "m3r_gn_begin",
+    "m3r_gn_linearize",
+    "m3r_gn_solve_retract",
+    "m3r_gn_edge_blocks",
+    "m3r_gn_iterations_done",
+]
+
+
+def check(rc, what):
+    if rc != M3R_OK:
+        msg = last_error()
+        raise RuntimeError(f"{what}: {msg.decode() if msg else 'error'} (code {rc})")

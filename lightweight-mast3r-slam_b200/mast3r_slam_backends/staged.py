@@ -1,0 +1,145 @@
+"""Staged and multi-GPU Gauss-Newton on top of the C ABI (m3r_gn_begin / m3r_gn_linearize /
+m3r_gn_solve_retract, include/m3r_backends.h).
+
+Multi-GPU: one process per GPU.  Every rank holds a replica of
+`Twc`, `Xs`, `Cs` and the full `ii`/`jj` lists, and the rows of `idx_ii2jj`, `valid_match`,
+`Q` for its contiguous shard of the directed edges.  Per iteration each rank linearises its
+shard into the dense fp64 system, the systems are summed with one all-reduce (NCCL over
+NVLink), and every rank runs the same Cholesky solve and retraction on its replica: the
+all-reduce result is identical on all ranks, so the replicas stay bitwise identical with no
+broadcast.  The reference has no multi-GPU path; this is new.
+"""
+import ctypes
+
+import torch
+
+from . import _lib, _workspace, _ptr, _stream
+from ._lib import GnProblem
+
+KINDS = {"rays": _lib.GN_RAYS, "calib": _lib.GN_CALIB, "points": _lib.GN_POINTS}
+
+
+def shard_range(num_edges, rank, world_size):
+    """Contiguous, near-equal split of the directed edges (all edges cost n points)."""
+    base, rem = divmod(num_edges, world_size)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+class StagedGN:
+    """One Gauss-Newton problem, driven stage by stage.
+
+    `idx_ii2jj`, `valid_match`, `Q` hold ONLY the rows [edge_begin, edge_end) of the graph's
+    directed edges; `ii`, `jj` are the whole lists."""
+
+    def __init__(self, kind, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, *, edge_begin=0,
+                 edge_end=None, K=None, height=0, width=0, pixel_border=0, z_eps=0.0,
+                 sigma_ray=1.0, sigma_dist=1.0, sigma_pixel=1.0, sigma_depth=1.0,
+                 sigma_point=1.0, C_thresh=0.0, Q_thresh=0.0):
+        for name, t in dict(Twc=Twc, Xs=Xs, Cs=Cs, ii=ii, jj=jj, idx_ii2jj=idx_ii2jj,
+                            valid_match=valid_match, Q=Q).items():
+            if not t.is_cuda:
+                raise RuntimeError(f"{name} must be a CUDA tensor")
+            if not t.is_contiguous():
+                raise RuntimeError(f"{name} must be contiguous")
+        self.dev = Twc.device
+        N, n, E = Xs.shape[0], Xs.shape[1], ii.shape[0]
+        if edge_end is None:
+            edge_end = E
+        rows = edge_end - edge_begin
+        if idx_ii2jj.numel() != rows * n or valid_match.numel() != rows * n or Q.numel() != rows * n:
+            raise RuntimeError("edge data must hold exactly the rows of this shard")
+        self.N, self.n, self.E = N, n, E
+        self.keep = (Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, K)  # keep storage alive
+        p = GnProblem()
+        p.kind = KINDS[kind]
+        p.num_poses, p.num_points, p.num_edges = N, n, E
+        p.edge_begin, p.edge_end = edge_begin, edge_end
+        p.Twc, p.Xs, p.Cs = Twc.data_ptr(), Xs.data_ptr(), Cs.data_ptr()
+        p.ii, p.jj = ii.data_ptr(), jj.data_ptr()
+        p.idx_ii2jj, p.valid_match, p.Q = idx_ii2jj.data_ptr(), valid_match.data_ptr(), Q.data_ptr()
+        p.sigma_ray, p.sigma_dist = sigma_ray, sigma_dist
+        p.K = K.data_ptr() if K is not None else None
+        p.height, p.width, p.pixel_border = int(height), int(width), int(pixel_border)
+        p.z_eps, p.sigma_pixel, p.sigma_depth = z_eps, sigma_pixel, sigma_depth
+        p.sigma_point = sigma_point
+        p.C_thresh, p.Q_thresh = C_thresh, Q_thresh
+        self.prob = p
+        self.ws = _workspace(self.dev)
+        self.D = 7 * (N - 1)
+        self.system = torch.empty(int(_lib.gn_system_size(N)), dtype=torch.float64, device=self.dev)
+        self.dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=self.dev)
+
+    def begin(self):
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.gn_begin(self.ws.handle, ctypes.byref(self.prob), _stream()), "gn_begin")
+
+    def linearize(self):
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.gn_linearize(self.ws.handle, ctypes.byref(self.prob),
+                                         _ptr(self.system), _stream()), "gn_linearize")
+
+    def solve_retract(self, delta_thresh=0.0):
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.gn_solve_retract(self.ws.handle, ctypes.byref(self.prob),
+                                             _ptr(self.system), _ptr(self.dx), float(delta_thresh),
+                                             _stream()), "gn_solve_retract")
+
+    def H(self):
+        """Dense [D,D] view of the assembled system (lower triangle meaningful)."""
+        return self.system[: self.D * self.D].view(self.D, self.D)
+
+    def b(self):
+        return self.system[self.D * self.D:]
+
+    def edge_blocks(self):
+        """(Hjj [E_shard,7,7], gj [E_shard,7]) fp64 copies of the last linearisation."""
+        hp, gp = ctypes.c_void_p(), ctypes.c_void_p()
+        _lib.check(_lib.gn_edge_blocks(self.ws.handle, ctypes.byref(hp), ctypes.byref(gp)),
+                   "gn_edge_blocks")
+        rows = self.prob.edge_end - self.prob.edge_begin
+        H = _from_ptr(hp.value, (rows, 7, 7), self.dev)
+        g = _from_ptr(gp.value, (rows, 7), self.dev)
+        return H.clone(), g.clone()
+
+    def iterations_done(self):
+        it = ctypes.c_int(0)
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.gn_iterations_done(self.ws.handle, _stream(), ctypes.byref(it)),
+                       "gn_iterations_done")
+        return it.value
+
+
+class _CudaArray:
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {
+            "shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+            "strides": None,
+        }
+
+
+def _from_ptr(ptr, shape, device):
+    with torch.cuda.device(device):
+        return torch.as_tensor(_CudaArray(ptr, shape, "<f8"), device=device)
+
+
+def gauss_newton_sharded(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_shard, *,
+                         max_iter, delta_thresh, group=None, **params):
+    """SPMD Gauss-Newton: call on every rank of `group` with the same replicated tensors and
+    this rank's shard of the edge data (rows `shard_range(E, rank, world)`).
+
+    Returns [dx]; Twc is updated in place on every rank (bitwise identical replicas)."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    begin, end = shard_range(ii.shape[0], rank, world)
+    gn = StagedGN(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_shard,
+                  edge_begin=begin, edge_end=end, **params)
+    gn.begin()
+    for _ in range(int(max_iter)):
+        gn.linearize()
+        if world > 1:
+            dist.all_reduce(gn.system, op=dist.ReduceOp.SUM, group=group)
+        gn.solve_retract(delta_thresh)
+    return [gn.dx], gn

@@ -1,0 +1,235 @@
+"""GPU parity tests of the Gauss-Newton exports (gauss_newton_rays / _calib / _points)
+through the drop-in module and the staged C ABI, against the CPU oracle, the golden vectors
+and, when oracle/_ref is present, the reference's own CUDA extension on the same device.
+
+Tolerance (BASELINE.json north_star): pose updates and final Sim(3) states within 1e-4
+relative in fp32.  "Relative" is taken against the magnitude of the compared quantity
+(||dx|| for the first step, max(1, |Twc|) for pose states)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from test_oracle import gn_params
+
+pytestmark = pytest.mark.gpu
+D = synth.GN_DEFAULTS
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+KINDS = ["rays", "calib", "points"]
+TOL = 1e-4
+
+
+def _call(mod, kind, g, Twc, max_iter, delta_thresh, dev="cuda"):
+    t = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in g.items()}
+    if kind == "rays":
+        return mod.gauss_newton_rays(Twc, t["Xs"], t["Cs"], t["ii"], t["jj"], t["idx_ii2jj"],
+                                     t["valid_match"], t["Q"], D["sigma_ray"], D["sigma_dist"],
+                                     D["C_thresh"], D["Q_thresh"], max_iter, delta_thresh)
+    if kind == "calib":
+        return mod.gauss_newton_calib(Twc, t["Xs"], t["Cs"], t["K"], t["ii"], t["jj"],
+                                      t["idx_ii2jj"], t["valid_match"], t["Q"], g["h"], g["w"],
+                                      D["pixel_border"], D["z_eps"], D["sigma_pixel"],
+                                      D["sigma_depth"], D["C_thresh"], D["Q_thresh"], max_iter,
+                                      delta_thresh)
+    return mod.gauss_newton_points(Twc, t["Xs"], t["Cs"], t["ii"], t["jj"], t["idx_ii2jj"],
+                                   t["valid_match"], t["Q"], D["sigma_point"], D["C_thresh"],
+                                   D["Q_thresh"], max_iter, delta_thresh)
+
+
+def _staged(kind, g, Twc, **kw):
+    from mast3r_slam_backends.staged import StagedGN
+
+    t = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in g.items()}
+    return StagedGN(kind, Twc, t["Xs"], t["Cs"], t["ii"], t["jj"], kw.pop("idx", t["idx_ii2jj"]),
+                    kw.pop("valid", t["valid_match"]), kw.pop("Q", t["Q"]), K=t["K"], height=g["h"],
+                    width=g["w"], pixel_border=D["pixel_border"], z_eps=D["z_eps"],
+                    sigma_ray=D["sigma_ray"], sigma_dist=D["sigma_dist"],
+                    sigma_pixel=D["sigma_pixel"], sigma_depth=D["sigma_depth"],
+                    sigma_point=D["sigma_point"], C_thresh=D["C_thresh"], Q_thresh=D["Q_thresh"], **kw)
+
+
+def _rel(a, b):
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def _pose_err(a, b):
+    return ((a - b).abs().max() / max(1.0, b.abs().max().item())).item()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("N,h,w,seed", [(4, 48, 64, 0), (7, 96, 128, 1), (5, 45, 53, 2)])
+def test_edge_blocks_vs_oracle(backends, oracle, kind, N, h, w, seed):
+    """Per-edge world-frame blocks: H_jj (and through Ji = -Jj all four blocks) and g_j."""
+    g = synth.make_graph(N, h, w, seed=seed)
+    Twc = g["Twc_init"].cuda().clone()
+    gn = _staged(kind, g, Twc)
+    gn.begin()
+    gn.linearize()
+    Hjj, gj = gn.edge_blocks()
+    Hs, gs = oracle.gn_accumulate(gn_params(oracle, kind, g), g["Twc_init"], g["Xs"], g["Cs"],
+                                  g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"])
+    Hjj, gj = Hjj.cpu(), gj.cpu()
+    scale = Hs[3].double().flatten(1).norm(dim=1).clamp_min(1e-30)
+    eH = ((Hjj - Hs[3].double()).flatten(1).norm(dim=1) / scale).max().item()
+    eHij = ((-Hjj - Hs[1].double()).flatten(1).norm(dim=1) / scale).max().item()
+    eg = ((gj - gs[1].double()).norm(dim=1) / gs[1].double().norm(dim=1).clamp_min(1e-30)).max().item()
+    print(f"{kind} N={N} {h}x{w}: max rel block error H_jj {eH:.2e}, H_ij {eHij:.2e}, g_j {eg:.2e}")
+    assert eH < TOL and eHij < TOL and eg < 10 * TOL  # g cancels (sum of signed terms)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("N,h,w,seed,stride", [(5, 48, 64, 0, 1), (9, 96, 128, 1, 3), (4, 45, 53, 2, 7)])
+def test_first_step_and_final_poses_vs_oracle(backends, oracle, kind, N, h, w, seed, stride):
+    g = synth.make_graph(N, h, w, seed=seed, kf_id_stride=stride)
+    P = gn_params(oracle, kind, g)
+    args = (g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"])
+    # one iteration: the pose update itself
+    Twc = g["Twc_init"].cuda().clone()
+    (dx,) = _call(backends, kind, g, Twc, 1, 0.0)
+    To, dxo, _ = oracle.gauss_newton(P, g["Twc_init"], *args, 1, 0.0)
+    e_dx, e_T1 = _rel(dx.cpu(), dxo), _pose_err(Twc.cpu(), To)
+    # the full solve
+    Twc10 = g["Twc_init"].cuda().clone()
+    (dx10,) = _call(backends, kind, g, Twc10, D["max_iter"], D["delta_thresh"])
+    To10, dxo10, _ = oracle.gauss_newton(P, g["Twc_init"], *args, D["max_iter"], D["delta_thresh"])
+    e_T10 = _pose_err(Twc10.cpu(), To10)
+    print(f"{kind} N={N} {h}x{w}: rel err dx(iter 1) {e_dx:.2e}, Twc after 1 {e_T1:.2e}, "
+          f"Twc after {D['max_iter']} {e_T10:.2e}")
+    assert dx.shape == (N - 1, 7) and torch.equal(Twc[0].cpu(), g["Twc_init"][0])
+    assert e_dx < TOL and e_T1 < TOL and e_T10 < TOL
+
+
+def test_failed_factorisation_gives_zero_step(backends):
+    """All matches invalid -> H = 0 -> Cholesky fails -> dx = 0 and Twc untouched
+    (gn_kernels.cu:147-150), never NaN."""
+    g = synth.make_graph(4, 32, 32, seed=3)
+    g["valid_match"] = torch.zeros_like(g["valid_match"])
+    for kind in KINDS:
+        Twc = g["Twc_init"].cuda().clone()
+        (dx,) = _call(backends, kind, g, Twc, 3, 1e-8)
+        assert (dx == 0).all() and torch.equal(Twc.cpu(), g["Twc_init"])
+
+
+def test_early_stop_and_iteration_count(backends):
+    g = synth.make_graph(4, 48, 64, seed=4)
+    Twc = g["Twc_init"].cuda().clone()
+    gn = _staged("points", g, Twc)
+    gn.begin()
+    for _ in range(5):
+        gn.linearize()
+        gn.solve_retract(delta_thresh=1e9)  # first step is below the threshold -> stop
+    assert gn.iterations_done() == 1
+    snap, dx1 = Twc.clone(), gn.dx.clone()
+    gn.linearize()
+    gn.solve_retract(1e9)
+    assert torch.equal(Twc, snap) and torch.equal(gn.dx, dx1)  # later launches are no-ops
+    Twc2 = g["Twc_init"].cuda().clone()
+    gn2 = _staged("points", g, Twc2)
+    gn2.begin()
+    for _ in range(4):
+        gn2.linearize()
+        gn2.solve_retract(0.0)
+    assert gn2.iterations_done() == 4
+
+
+def test_zero_residual_fixed_point(backends):
+    """Noise-free consistent pointmaps at the true poses with matches that are exact: build
+    X_j := T_j^-1 T_i X_i[idx] so every residual vanishes -> dx = 0 to rounding."""
+    g = synth.make_graph(3, 32, 40, seed=5, point_noise=0.0)
+    T = g["Twc_true"].double()
+    Xs = g["Xs"].double().clone()
+    # make keyframes 1,2 exact copies of keyframe 0's geometry through identity matches
+    n = g["n"]
+    for k in (1, 2):
+        Pw = synth.sim3_act(T[0], Xs[0])
+        Xs[k] = synth.sim3_inv_act(T[k], Pw)
+    g["Xs"] = Xs.float()
+    g["idx_ii2jj"] = torch.arange(n).repeat(g["E"], 1)
+    g["valid_match"] = torch.ones_like(g["valid_match"])
+    for kind in ("rays", "points"):
+        Twc = g["Twc_true"].cuda().clone()
+        (dx,) = _call(backends, kind, g, Twc, 1, 0.0)
+        assert dx.abs().max() < 2e-5, (kind, dx.abs().max())
+        assert (Twc.cpu() - g["Twc_true"]).abs().max() < 2e-5
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_sharded_systems_sum_to_unsharded(backends, kind):
+    """Multi-GPU path on one device: linearising two edge shards separately and summing the
+    systems (what the all-reduce does) reproduces the unsharded system, and the solve from
+    the summed system matches the single call."""
+    from mast3r_slam_backends.staged import shard_range
+
+    g = synth.make_graph(6, 48, 64, seed=6)
+    E, n = g["E"], g["n"]
+    Twc = g["Twc_init"].cuda().clone()
+    full = _staged(kind, g, Twc)
+    full.begin()
+    full.linearize()
+    ref_sys = full.system.clone()
+    total = torch.zeros_like(ref_sys)
+    for r in range(2):
+        b0, b1 = shard_range(E, r, 2)
+        sh = _staged(kind, g, Twc, idx=g["idx_ii2jj"][b0:b1].contiguous().cuda(),
+                     valid=g["valid_match"][b0:b1].contiguous().cuda(),
+                     Q=g["Q"][b0:b1].contiguous().cuda(), edge_begin=b0, edge_end=b1)
+        sh.begin()
+        sh.linearize()
+        total += sh.system
+    Dm = full.D
+    Hf, Ht = ref_sys[:Dm * Dm].view(Dm, Dm), total[:Dm * Dm].view(Dm, Dm)
+    assert (Ht - Hf).abs().max() <= 1e-12 * Hf.abs().max()
+    assert (total[Dm * Dm:] - ref_sys[Dm * Dm:]).abs().max() <= 1e-9 * ref_sys[Dm * Dm:].abs().max() + 1e-12
+    assert torch.equal(torch.triu(Hf, 1), torch.zeros_like(Hf))  # strictly upper part stays zero
+
+
+def test_argument_errors(backends):
+    g = synth.make_graph(3, 16, 16, seed=7)
+    Twc = g["Twc_init"].cuda().clone()
+    bad = dict(g)
+    bad["Xs"] = g["Xs"].cuda().transpose(1, 2)  # non-contiguous
+    with pytest.raises(RuntimeError, match="must be contiguous"):
+        _call(backends, "rays", bad, Twc, 1, 0.0)
+    with pytest.raises(RuntimeError):
+        _call(backends, "rays", g, Twc, 1, 0.0, dev="cpu")
+
+
+# ------------------------------------------------------------------------------ reference CUDA
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("N,h,w,seed", [(5, 48, 64, 0), (8, 96, 128, 1), (16, 192, 256, 2)])
+def test_vs_reference_cuda(backends, refcuda, kind, N, h, w, seed):
+    if refcuda is None:
+        pytest.skip("oracle/_ref/mast3r_slam_backends_ref.so not built")
+    g = synth.make_graph(N, h, w, seed=seed, device="cuda")
+    Ta, Tb = g["Twc_init"].clone(), g["Twc_init"].clone()
+    (dx,) = _call(backends, kind, g, Ta, 1, 0.0)
+    (rdx,) = _call(refcuda, kind, g, Tb, 1, 0.0)
+    e_dx, e_T1 = _rel(dx, rdx), _pose_err(Ta, Tb)
+    Ta, Tb = g["Twc_init"].clone(), g["Twc_init"].clone()
+    _call(backends, kind, g, Ta, D["max_iter"], D["delta_thresh"])
+    _call(refcuda, kind, g, Tb, D["max_iter"], D["delta_thresh"])
+    e_T = _pose_err(Ta, Tb)
+    print(f"vs reference CUDA {kind} N={N} {h}x{w}: rel err dx(iter 1) {e_dx:.2e}, "
+          f"Twc after 1 {e_T1:.2e}, Twc after {D['max_iter']} {e_T:.2e}")
+    assert e_dx < TOL and e_T1 < TOL and e_T < TOL
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "gn_*.npz"))) or [None])
+def test_golden_gn_gpu(backends, path):
+    if path is None:
+        pytest.skip("no golden GN vectors committed yet")
+    z = np.load(path)
+    kind = str(z["kind"])
+    g = dict(Xs=torch.from_numpy(z["Xs"]), Cs=torch.from_numpy(z["Cs"]), K=torch.from_numpy(z["K"]),
+             ii=torch.from_numpy(z["ii"]), jj=torch.from_numpy(z["jj"]),
+             idx_ii2jj=torch.from_numpy(z["idx"]), valid_match=torch.from_numpy(z["valid"]).bool(),
+             Q=torch.from_numpy(z["Q"]), h=int(z["height"]), w=int(z["width"]))
+    for iters, key in ((1, "ref_1"), (int(z["max_iter"]), "ref_full")):
+        Twc = torch.from_numpy(z["Twc"]).cuda().clone()
+        (dx,) = _call(backends, kind, g, Twc, iters, float(z["delta_thresh"]))
+        assert _pose_err(Twc.cpu(), torch.from_numpy(z[key + "_Twc"])) < TOL
+        if iters == 1:
+            assert _rel(dx.cpu(), torch.from_numpy(z[key + "_dx"])) < TOL
