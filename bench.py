@@ -399,6 +399,9 @@ def main():
     ap.add_argument("--skip-gn", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-refcuda", action="store_true")
+    ap.add_argument("--profile", action="store_true",
+                    help="wrap the timed regions in cudaProfilerStart/Stop (for ncu --profile-from-start off)")
+    ap.add_argument("--iter-proj-variant", type=int, default=0)
     args = ap.parse_args()
     rank, local_rank, world = dist_env()
     if args.impl == "reference":
@@ -426,7 +429,12 @@ def main():
     time_matching(be, sets, M, 20, 5, world)  # clocks up
     sampler.start()
     l0 = _lib.launch_count()
+    if args.profile:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     r = time_matching(be, sets, M, args.steps, args.warmup, world)
+    if args.profile:
+        torch.cuda.profiler.stop()
     launches = (_lib.launch_count() - l0) - 2 * args.warmup
     clocks = sampler.stop()
     ms_step = r["total_ms"] / args.steps
@@ -471,8 +479,13 @@ def main():
     if not args.skip_gn:
         g = make_gn_graph(args.gn_keyframes, "cuda", seed=0)
         l0 = _lib.launch_count()
-        gr = time_gn(g, D, args.gn_kind, rank, world)
-        gn_launches = (_lib.launch_count() - l0) // 4
+        if args.profile:
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
+        gr = time_gn(g, D, args.gn_kind, rank, world, reps=1 if args.profile else 3)
+        if args.profile:
+            torch.cuda.profiler.stop()
+        gn_launches = (_lib.launch_count() - l0) // (2 if args.profile else 4)
         E, n, N = g["E"], g["n"], g["N"]
         gn_bytes = B_GN * E * n + 840 * E + 32 * N
         lin_gbs = gn_bytes / world / (gr["linearize_ms"] * 1e-3) / 1e9

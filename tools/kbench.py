@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""Kernel micro-timings on the B200 (CUDA events, L2-cold rotation): variants side by side."""
+import os, sys, statistics
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in ("lightweight-mast3r-slam_b200", "oracle", "tests"):
+    sys.path.insert(0, os.path.join(ROOT, p))
+sys.path.insert(0, ROOT)
+import torch
+import bench, synth
+import mast3r_slam_backends as be
+
+M = synth.MATCH_DEFAULTS
+
+
+def timeit(fn, sets, reps=40, warm=5):
+    for i in range(warm):
+        fn(sets[i % len(sets)])
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for i in range(reps):
+        ev[i][0].record(); fn(sets[i % len(sets)]); ev[i][1].record()
+    torch.cuda.synchronize()
+    t = [a.elapsed_time(b) for a, b in ev]
+    return statistics.median(t) * 1e3, min(t) * 1e3
+
+
+def main():
+    sets = bench.make_match_sets("cuda", 8)
+    for s in sets:
+        p, _ = be.iter_proj(s["rays"], s["pts"], s["p_init"], 10, 1e-8, 1e-6)
+        s["p1"] = p.long()
+    for v in (1, 2):
+        med, mn = timeit(lambda s: be.iter_proj(s["rays"], s["pts"], s["p_init"], 10, 1e-8, 1e-6, _variant=v), sets)
+        print(f"iter_proj variant {v}: median {med:.1f} us, min {mn:.1f} us")
+    for v in (0, 1):
+        med, mn = timeit(lambda s: be.refine_matches(s["D11"], s["D21"], s["p1"], 3, 5, _variant=v), sets)
+        print(f"refine_matches variant {v}: median {med:.1f} us, min {mn:.1f} us")
+    for extra in sys.argv[1:]:
+        pass
+
+
+if __name__ == "__main__":
+    main()
