@@ -23,6 +23,11 @@
 //    the remaining enqueued kernels exit at their first instruction.
 #include "m3r_common.cuh"
 
+#include <cooperative_groups.h>
+
+#include <cstdlib>
+#include <cstring>
+
 namespace m3r {
 
 // ----------------------------------------------------------------------------------------
@@ -720,6 +725,67 @@ __device__ void exp_sim3(const float xi[7], float t[3], float q[4], float &s) {
   t[0] += B * tau[0], t[1] += B * tau[1], t[2] += B * tau[2];
 }
 
+// dx = -x, left retraction, stop test: the tail of every solve kernel (NT threads of one CTA)
+template <int NT>
+__device__ void finish_step(const int t, const bool fail, const int D, const double *xbuf,
+                            float *__restrict__ Twc, float *__restrict__ dx, const int num_poses,
+                            const float delta_thresh, int *__restrict__ flags) {
+  __shared__ double redn[NT / 32];
+  // dx = -x (zeros when the factorisation failed or produced non-finite values)
+  __shared__ int nonfinite;
+  if (t == 0) nonfinite = 0;
+  __syncthreads();
+  if (!fail) {
+    int bad = 0;
+    for (int k = t; k < D; k += NT)
+      if (!isfinite(xbuf[k])) bad = 1;
+    if (bad) nonfinite = 1;
+  }
+  __syncthreads();
+  const bool zero_step = fail || nonfinite;
+  double nrm = 0.0;
+  for (int k = t; k < D; k += NT) {
+    const float d = zero_step ? 0.0f : static_cast<float>(-xbuf[k]);
+    dx[k] = d;
+    nrm += static_cast<double>(d) * static_cast<double>(d);
+  }
+  __syncthreads();
+
+  // left retraction of poses 1..N-1 (pose_retr_kernel :415-453, retrSim3 :392-413)
+  for (int k = 1 + t; k < num_poses; k += NT) {
+    float xi[7];
+#pragma unroll
+    for (int m = 0; m < 7; m++) xi[m] = dx[(k - 1) * 7 + m];
+    float *P = Twc + k * 8;
+    const float tt[3] = {P[0], P[1], P[2]};
+    const float q[4] = {P[3], P[4], P[5], P[6]};
+    const float s = P[7];
+    float dt[3], dq[4], ds;
+    exp_sim3(xi, dt, dq, ds);
+    float q1[4], t1[3];
+    quat_mul(dq, q, q1);
+    act_so3<float>(dq, tt, t1);
+    P[0] = t1[0] * ds + dt[0];
+    P[1] = t1[1] * ds + dt[1];
+    P[2] = t1[2] * ds + dt[2];
+    P[3] = q1[0], P[4] = q1[1], P[5] = q1[2], P[6] = q1[3];
+    P[7] = ds * s;
+  }
+
+  // stop test (:1219-1222)
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, off);
+  if ((t & 31) == 0) redn[t >> 5] = nrm;
+  __syncthreads();
+  if (t == 0) {
+    double s = 0.0;
+    for (int k = 0; k < NT / 32; k++) s += redn[k];
+    flags[1] += 1;  // iterations executed
+    flags[2] = 0;   // clear the failure flag for the next iteration
+    if (static_cast<float>(sqrt(s)) < delta_thresh) flags[0] = 1;
+  }
+}
+
 constexpr int kSolveThreads = 512;
 
 __global__ void __launch_bounds__(kSolveThreads)
@@ -732,7 +798,6 @@ __global__ void __launch_bounds__(kSolveThreads)
   const double *L = sys;
   const double *rhs = sys + static_cast<size_t>(D) * D;
   __shared__ double xs[kPB];
-  __shared__ double redn[kSolveThreads / 32];
   const bool fail = flags[2] != 0;
 
   if (!fail) {
@@ -794,60 +859,10 @@ __global__ void __launch_bounds__(kSolveThreads)
     }
   }
 
-  // dx = -x (zeros when the factorisation failed or produced non-finite values)
-  __shared__ int nonfinite;
-  if (t == 0) nonfinite = 0;
-  __syncthreads();
-  if (!fail) {
-    int bad = 0;
-    for (int k = t; k < D; k += kSolveThreads)
-      if (!isfinite(xbuf[k])) bad = 1;
-    if (bad) nonfinite = 1;
-  }
-  __syncthreads();
-  const bool zero_step = fail || nonfinite;
-  double nrm = 0.0;
-  for (int k = t; k < D; k += kSolveThreads) {
-    const float d = zero_step ? 0.0f : static_cast<float>(-xbuf[k]);
-    dx[k] = d;
-    nrm += static_cast<double>(d) * static_cast<double>(d);
-  }
-  __syncthreads();
-
-  // left retraction of poses 1..N-1 (pose_retr_kernel :415-453, retrSim3 :392-413)
-  for (int k = 1 + t; k < num_poses; k += kSolveThreads) {
-    float xi[7];
-#pragma unroll
-    for (int m = 0; m < 7; m++) xi[m] = dx[(k - 1) * 7 + m];
-    float *P = Twc + k * 8;
-    const float tt[3] = {P[0], P[1], P[2]};
-    const float q[4] = {P[3], P[4], P[5], P[6]};
-    const float s = P[7];
-    float dt[3], dq[4], ds;
-    exp_sim3(xi, dt, dq, ds);
-    float q1[4], t1[3];
-    quat_mul(dq, q, q1);
-    act_so3<float>(dq, tt, t1);
-    P[0] = t1[0] * ds + dt[0];
-    P[1] = t1[1] * ds + dt[1];
-    P[2] = t1[2] * ds + dt[2];
-    P[3] = q1[0], P[4] = q1[1], P[5] = q1[2], P[6] = q1[3];
-    P[7] = ds * s;
-  }
-
-  // stop test (:1219-1222)
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, off);
-  if ((t & 31) == 0) redn[t >> 5] = nrm;
-  __syncthreads();
-  if (t == 0) {
-    double s = 0.0;
-    for (int k = 0; k < kSolveThreads / 32; k++) s += redn[k];
-    flags[1] += 1;  // iterations executed
-    flags[2] = 0;   // clear the failure flag for the next iteration
-    if (static_cast<float>(sqrt(s)) < delta_thresh) flags[0] = 1;
-  }
+  finish_step<kSolveThreads>(t, fail, D, xbuf, Twc, dx, num_poses, delta_thresh, flags);
 }
+
+#include "gn_chol_coop.cuh"
 
 // ----------------------------------------------------------------------------------------
 // keyframe id -> packed pose index (sorted-unique rank), no host sync
@@ -1099,7 +1114,44 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int D = 7 * (prob->num_poses - 1);
   if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
-  if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kPB * kPB))) return rc;
+  if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride))) return rc;
+  static const bool use_multi = [] {
+    const char *e = getenv("M3R_GN_SOLVER");
+    return e && strcmp(e, "multi") == 0;
+  }();
+  if (!use_multi) {
+    // one cooperative launch: Cholesky + substitutions + retraction + stop test
+    static int max_coresident = 0;
+    if (max_coresident == 0) {
+      int dev = 0, sms = 0, per_sm = 0;
+      M3R_CUDA_TRY(cudaGetDevice(&dev));
+      M3R_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      M3R_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_chol_solve_coop_kernel,
+                                                                kCoopThreads, 0));
+      max_coresident = sms * (per_sm > 0 ? 1 : 0);  // one CTA per SM keeps the barrier cheap
+      if (max_coresident <= 0) {
+        set_error("gn_solve_retract: cooperative kernel cannot be resident");
+        return M3R_ERR_CUDA;
+      }
+    }
+    const int m0 = D - kPB > 0 ? D - kPB : 0;
+    const int T0 = (m0 + 31) / 32;  // 32x32 tiles of the first trailing update
+    int want = T0 * (T0 + 1) / 2;
+    const int row_ctas = (m0 + kTrsmRows - 1) / kTrsmRows;
+    if (want < row_ctas) want = row_ctas;
+    if (want < 1) want = 1;
+    const int grid = want < max_coresident ? want : max_coresident;
+    double *sys_p = system, *ld_p = ws->ldiag.p, *x_p = ws->xbuf.p;
+    float *twc_p = prob->Twc, *dx_p = dx;
+    int D_ = D, np = prob->num_poses;
+    float dth = delta_thresh;
+    int *fl = ws->flags;
+    void *args[] = {&sys_p, &ld_p, &D_, &x_p, &twc_p, &dx_p, &np, &dth, &fl};
+    M3R_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(gn_chol_solve_coop_kernel),
+                                             dim3(grid), dim3(kCoopThreads), args, 0, s));
+    g_launch_count.fetch_add(1, std::memory_order_relaxed);
+    return M3R_OK;
+  }
   for (int k0 = 0; k0 < D; k0 += kPB) {
     const int rows_below = D - k0 - kPB;
     const int pblocks = rows_below > 0 ? (rows_below + 63) / 64 : 1;
@@ -1115,6 +1167,15 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
                                                       prob->Twc, dx, prob->num_poses,
                                                       delta_thresh, ws->flags);
   M3R_LAUNCH_CHECK("gn_solve_retract_kernel");
+  return M3R_OK;
+}
+
+// debug: cumulative per-phase cycle counts of the cooperative solver (CTA 0), then reset
+extern "C" int m3r_debug_coop_profile(long long *out8) {
+  long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  M3R_CUDA_TRY(cudaDeviceSynchronize());
+  M3R_CUDA_TRY(cudaMemcpyFromSymbol(out8, g_coop_prof, sizeof(zero)));
+  M3R_CUDA_TRY(cudaMemcpyToSymbol(g_coop_prof, zero, sizeof(zero)));
   return M3R_OK;
 }
 
