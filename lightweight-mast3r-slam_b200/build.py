@@ -18,8 +18,9 @@ def needs_build():
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
-    deps = SRC + [os.path.join(HERE, "csrc", "m3r_common.cuh"),
-                  os.path.join(os.path.dirname(HERE), "include", "m3r_backends.h")]
+    csrc = os.path.join(HERE, "csrc")
+    deps = [os.path.join(csrc, f) for f in os.listdir(csrc)] + [
+        os.path.join(os.path.dirname(HERE), "include", "m3r_backends.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
