@@ -2,10 +2,12 @@
 //
 // Replaces the reference's matching_kernels.cu (iter_proj_kernel :119-275,
 // refine_matches_kernel :25-81) behind the C ABI of include/m3r_backends.h.  Written from
-// the behaviour of those kernels, not from their code: one warp handles 32 neighbouring
-// query points and stages the ray-image texels they touch through shared memory; the
+// the behaviour of those kernels, not from their code: iter_proj memoises its pure
+// evaluations (one gather per LM iteration at most, none once a point has converged); the
 // descriptor search runs two candidates per half2 lane with per-operation rounding.
 #include <cuda_fp16.h>
+
+#include <climits>
 
 #include "m3r_common.cuh"
 
@@ -75,170 +77,129 @@ __device__ __forceinline__ void eval_at(Fetch fetch, float u, float v, const flo
   cost = err[0] * err[0] + err[1] * err[1] + err[2] * err[2];
 }
 
-// Per-warp staging of the texels a gather touches.  The 32 lanes of a warp hold
-// neighbouring query points, whose 2x2 bilinear footprints overlap and sit on at most a few
-// image rows while the match field is smooth.  The warp copies the bounding box of all
-// footprints from global (coalesced, every 128-byte line once) into its shared-memory tile
-// and the lanes then read their corners from there: with the [h,w,9] layout the API fixes
-// (36-byte texels, only 4-byte aligned) a direct per-lane gather touches ~9 lines per load
-// instruction, the staged copy ~1.3.  If the box does not fit the tile (arbitrary p_init),
-// the warp falls back to direct global loads for that gather: same values either way.
-constexpr int kIpWarps = 4;             // warps per CTA
-constexpr int kIpTileFloats = 1728;     // per-warp tile: 192 texels * 9 floats = 6912 B
-
-struct WarpTile {
-  float *smem;   // this warp's tile
-  int umin, vmin, wt, ht;
-  bool staged;
+// Gather of the four bilinear corners straight from the [h,w,9] image the API fixes
+// (36-byte texels, only 4-byte aligned, so no vector loads).  The whole image (7 MB at
+// 512x384) lives in L2; what the kernel has to economise is the number of gathers.
+struct GlobalFetch {
+  const float *img;
+  int w;
+  template <int NC>
+  __device__ __forceinline__ void operator()(int uu, int vv, float *out) const {
+    const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
+#pragma unroll
+    for (int c = 0; c < NC; c++) out[c] = __ldg(s + c);
+  }
 };
 
-template <int NCH>  // channels needed per texel: 9 (ray+grads) or 3 (ray only)
-__device__ __forceinline__ WarpTile stage_tile(const float *__restrict__ img, int w, float *tile,
-                                               int u11, int v11, int lane) {
-  WarpTile t;
-  t.smem = tile;
-  const int umin = __reduce_min_sync(0xffffffffu, u11);
-  const int umax = __reduce_max_sync(0xffffffffu, u11) + 1;
-  const int vmin = __reduce_min_sync(0xffffffffu, v11);
-  const int vmax = __reduce_max_sync(0xffffffffu, v11) + 1;
-  t.umin = umin;
-  t.vmin = vmin;
-  t.wt = umax - umin + 1;
-  t.ht = vmax - vmin + 1;
-  t.staged = (t.wt * t.ht * 9 <= kIpTileFloats);
-  if (t.staged) {
-    __syncwarp();  // previous readers of the tile are done
-    const int row_floats = t.wt * 9;
-    for (int rrow = 0; rrow < t.ht; rrow++) {
-      const float *src = img + (static_cast<size_t>(vmin + rrow) * w + umin) * 9;
-      float *dst = tile + rrow * row_floats;
-      if (NCH == 9) {
-        for (int k = lane; k < row_floats; k += 32) dst[k] = __ldg(src + k);
-      } else {
-        // only channels 0..2 of each texel
-        for (int k = lane; k < t.wt * 3; k += 32) {
-          const int tx = k / 3, ch = k - tx * 3;
-          dst[tx * 9 + ch] = __ldg(src + tx * 9 + ch);
-        }
-      }
-    }
-    __syncwarp();
-  }
-  return t;
+// 2x2 normal equations with the LM diagonal and the clamped trial pixel (:202-222)
+__device__ __forceinline__ void lm_step(const float gx[3], const float gy[3], const float err[3],
+                                        float lambda, float u, float v, float u_hi, float v_hi,
+                                        float &u_new, float &v_new) {
+  float A00 = gx[0] * gx[0] + gx[1] * gx[1] + gx[2] * gx[2];
+  const float A01 = gx[0] * gy[0] + gx[1] * gy[1] + gx[2] * gy[2];
+  float A11 = gy[0] * gy[0] + gy[1] * gy[1] + gy[2] * gy[2];
+  const float b0 = -(err[0] * gx[0] + err[1] * gx[1] + err[2] * gx[2]);
+  const float b1 = -(err[0] * gy[0] + err[1] * gy[1] + err[2] * gy[2]);
+  A00 += lambda;
+  A11 += lambda;
+  const float det_inv = __frcp_rn(A00 * A11 - A01 * A01);
+  const float delta_u = det_inv * (A11 * b0 - A01 * b1);
+  const float delta_v = det_inv * (-A01 * b0 + A00 * b1);
+  u_new = clampf(u + delta_u, 1.0f, u_hi);
+  v_new = clampf(v + delta_v, 1.0f, v_hi);
 }
 
-template <bool kStaged>
-__global__ void __launch_bounds__(kIpWarps * 32)
+constexpr int kIpThreads = 128;
+
+// MODE 1: every iteration evaluates the current pixel (9 channels) and the trial pixel
+// (3 channels), as the reference kernel does: two gathers per iteration.
+//
+// MODE 0 (default): the same arithmetic with the evaluations memoised.  An evaluation is a
+// pure function of (u,v), so
+//   * the trial evaluation fetches all 9 channels; if the step is accepted it IS the next
+//     iteration's evaluation of the current pixel (bitwise), if rejected the current one is kept;
+//   * a trial pixel equal to the current pixel, or to the last rejected trial while the current
+//     pixel has not moved, has a known cost and is not fetched again.
+// After convergence (2-4 iterations on smooth maps) the LM step is below half an ulp of the
+// coordinate and the remaining iterations touch no memory.  At most one gather per iteration,
+// typically 3-4 per point instead of 20; results are bit-identical to MODE 1.
+template <int MODE>
+__global__ void __launch_bounds__(kIpThreads)
     iter_proj_kernel(const float *__restrict__ rays, const float *__restrict__ pts,
                      const float *__restrict__ p_init, float *__restrict__ p_new,
                      uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,
                      float lambda_init, float cost_thresh) {
-  __shared__ float tiles[kStaged ? kIpWarps * kIpTileFloats : 1];
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
   const int b = blockIdx.y;
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool active = idx < n;
-  if (!active) idx = n - 1;  // inactive lanes shadow the last point (keeps warps whole)
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
   const size_t gi = static_cast<size_t>(b) * n + idx;
-  const float *img = rays + static_cast<size_t>(b) * h * w * 9;
-  float *tile = tiles + (kStaged ? warp * kIpTileFloats : 0);
+  const GlobalFetch fetch{rays + static_cast<size_t>(b) * h * w * 9, w};
+  auto f9 = [&](int uu, int vv, float *out) { fetch.template operator()<9>(uu, vv, out); };
+  auto f3 = [&](int uu, int vv, float *out) { fetch.template operator()<3>(uu, vv, out); };
 
-  float u = __ldg(p_init + gi * 2 + 0);
-  float v = __ldg(p_init + gi * 2 + 1);
+  const float2 p0 = __ldg(reinterpret_cast<const float2 *>(p_init) + gi);
   const float pt[3] = {__ldg(pts + gi * 3 + 0), __ldg(pts + gi * 3 + 1), __ldg(pts + gi * 3 + 2)};
-  u = clampf(u, 1.0f, static_cast<float>(w - 2));
-  v = clampf(v, 1.0f, static_cast<float>(h - 2));
+  const float u_hi = static_cast<float>(w - 2), v_hi = static_cast<float>(h - 2);
+  float u = clampf(p0.x, 1.0f, u_hi);
+  float v = clampf(p0.y, 1.0f, v_hi);
 
   float lambda = lambda_init;
   bool conv = false;
-  for (int it = 0; it < max_iter; it++) {
+  if (MODE == 1) {
+    for (int it = 0; it < max_iter; it++) {
+      float gx[3], gy[3], err[3], cost;
+      eval_at<true>(f9, u, v, pt, gx, gy, err, cost);
+      float u_new, v_new;
+      lm_step(gx, gy, err, lambda, u, v, u_hi, v_hi, u_new, v_new);
+      float err2[3], new_cost;  // cost at the trial pixel, ray channels only (:225-256)
+      eval_at<false>(f3, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+      if (new_cost < cost) {  // accept (:259-264)
+        u = u_new;
+        v = v_new;
+        lambda = static_cast<float>(static_cast<double>(lambda) * 0.1);
+        conv = new_cost < cost_thresh;
+      } else {  // reject (:265-268)
+        lambda = lambda * 10.0f;
+        conv = cost < cost_thresh;
+      }
+    }
+  } else if (max_iter > 0) {
     float gx[3], gy[3], err[3], cost;
-    if (kStaged) {
-      const WarpTile t = stage_tile<9>(img, w, tile, static_cast<int>(floorf(u)),
-                                       static_cast<int>(floorf(v)), lane);
-      if (t.staged) {
-        auto fetch = [&](int uu, int vv, float *out) {
-          const float *s = t.smem + ((vv - t.vmin) * t.wt + (uu - t.umin)) * 9;
-#pragma unroll
-          for (int c = 0; c < 9; c++) out[c] = s[c];
-        };
-        eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
+    eval_at<true>(f9, u, v, pt, gx, gy, err, cost);
+    float ut = 0.f, vt = 0.f, cost_t = 0.f;  // last rejected trial since the pixel last moved
+    bool have_trial = false;
+    for (int it = 0; it < max_iter; it++) {
+      float u_new, v_new;
+      lm_step(gx, gy, err, lambda, u, v, u_hi, v_hi, u_new, v_new);
+      float ngx[3], ngy[3], nerr[3], new_cost;
+      bool fresh = false;
+      if (u_new == u && v_new == v) {
+        new_cost = cost;
+      } else if (have_trial && u_new == ut && v_new == vt) {
+        new_cost = cost_t;
       } else {
-        auto fetch = [&](int uu, int vv, float *out) {
-          const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
-#pragma unroll
-          for (int c = 0; c < 9; c++) out[c] = __ldg(s + c);
-        };
-        eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
+        eval_at<true>(f9, u_new, v_new, pt, ngx, ngy, nerr, new_cost);
+        fresh = true;
       }
-    } else {
-      auto fetch = [&](int uu, int vv, float *out) {
-        const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
+      // a memoised cost is never below `cost` (it was rejected against the same `cost`)
+      if (fresh && new_cost < cost) {
+        u = u_new;
+        v = v_new;
+        cost = new_cost;
 #pragma unroll
-        for (int c = 0; c < 9; c++) out[c] = __ldg(s + c);
-      };
-      eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
-    }
-
-    // 2x2 normal equations with the LM diagonal (:202-215)
-    float A00 = gx[0] * gx[0] + gx[1] * gx[1] + gx[2] * gx[2];
-    const float A01 = gx[0] * gy[0] + gx[1] * gy[1] + gx[2] * gy[2];
-    float A11 = gy[0] * gy[0] + gy[1] * gy[1] + gy[2] * gy[2];
-    const float b0 = -(err[0] * gx[0] + err[1] * gx[1] + err[2] * gx[2]);
-    const float b1 = -(err[0] * gy[0] + err[1] * gy[1] + err[2] * gy[2]);
-    A00 += lambda;
-    A11 += lambda;
-    const float det_inv = __frcp_rn(A00 * A11 - A01 * A01);
-    const float delta_u = det_inv * (A11 * b0 - A01 * b1);
-    const float delta_v = det_inv * (-A01 * b0 + A00 * b1);
-    const float u_new = clampf(u + delta_u, 1.0f, static_cast<float>(w - 2));
-    const float v_new = clampf(v + delta_v, 1.0f, static_cast<float>(h - 2));
-
-    // cost at the trial pixel, ray channels only (:225-256)
-    float err2[3], new_cost;
-    if (kStaged) {
-      const WarpTile t = stage_tile<3>(img, w, tile, static_cast<int>(floorf(u_new)),
-                                       static_cast<int>(floorf(v_new)), lane);
-      if (t.staged) {
-        auto fetch = [&](int uu, int vv, float *out) {
-          const float *s = t.smem + ((vv - t.vmin) * t.wt + (uu - t.umin)) * 9;
-#pragma unroll
-          for (int c = 0; c < 3; c++) out[c] = s[c];
-        };
-        eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+        for (int j = 0; j < 3; j++) gx[j] = ngx[j], gy[j] = ngy[j], err[j] = nerr[j];
+        have_trial = false;
+        lambda = static_cast<float>(static_cast<double>(lambda) * 0.1);
+        conv = new_cost < cost_thresh;
       } else {
-        auto fetch = [&](int uu, int vv, float *out) {
-          const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
-#pragma unroll
-          for (int c = 0; c < 3; c++) out[c] = __ldg(s + c);
-        };
-        eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+        ut = u_new, vt = v_new, cost_t = new_cost, have_trial = true;
+        lambda = lambda * 10.0f;
+        conv = cost < cost_thresh;
       }
-    } else {
-      auto fetch = [&](int uu, int vv, float *out) {
-        const float *s = img + (static_cast<size_t>(vv) * w + uu) * 9;
-#pragma unroll
-        for (int c = 0; c < 3; c++) out[c] = __ldg(s + c);
-      };
-      eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
-    }
-
-    if (new_cost < cost) {  // accept (:259-264)
-      u = u_new;
-      v = v_new;
-      lambda = static_cast<float>(static_cast<double>(lambda) * 0.1);
-      conv = new_cost < cost_thresh;
-    } else {  // reject (:265-268)
-      lambda = lambda * 10.0f;
-      conv = cost < cost_thresh;
     }
   }
-
-  if (active) {
-    reinterpret_cast<float2 *>(p_new)[gi] = make_float2(u, v);
-    converged[gi] = conv ? 1 : 0;
-  }
+  reinterpret_cast<float2 *>(p_new)[gi] = make_float2(u, v);
+  converged[gi] = conv ? 1 : 0;
 }
 
 // =========================================================================================
@@ -361,6 +322,220 @@ __global__ void __launch_bounds__(kRefineThreads)
       make_longlong2(static_cast<long long>(u_new), static_cast<long long>(v_new));
 }
 
+// -----------------------------------------------------------------------------------------
+// Tiled kernel (default for f16, fdim 24, radius 3, one query per pixel of an h x w grid).
+//
+// A CTA owns a 16x16 tile of query pixels.  While the match field is smooth the 245 candidate
+// windows of those 256 queries all fall inside one 48x48-texel box of D11 (110.6 KB): the CTA
+// fetches that box ONCE with TMA bulk copies (cp.async.bulk global->shared, one per tile row,
+// completion on an mbarrier) and every candidate row is then three conflict-free LDS.128
+// (48-byte rows: 8 consecutive lanes cover all 32 banks).  The direct kernel above re-reads
+// every candidate row through L1 (53 % hit rate, the rest from L2).
+//
+// Per dilation level a warp votes: if every lane's 7x7 window lies inside the staged box the
+// level runs fully unrolled from shared memory (out-of-image candidates are masked, the box's
+// out-of-image rows are simply never written); otherwise that warp runs the level with the
+// checked per-candidate path from global memory.  Same candidates, same order, same
+// arithmetic: results are identical either way.
+constexpr int kRtQ = 16;                    // query tile edge
+constexpr int kRtT = 48;                    // staged box edge (texels)
+constexpr int kRtThreads = kRtQ * kRtQ;     // 256
+constexpr int kRtRowU4 = 3;                 // uint4 per 24-half descriptor row
+constexpr int kRtTileBytes = kRtT * kRtT * kRtRowU4 * 16;
+constexpr int kRtSmemBytes = kRtTileBytes + 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// scores of two candidate rows against the query: lanes of the result = (row a, row b)
+__device__ __forceinline__ __half2 score_pair(const uint4 *ra, const uint4 *rb,
+                                              const uint32_t q[12]) {
+  uint32_t wa[12], wb[12];
+#pragma unroll
+  for (int i = 0; i < kRtRowU4; i++) {
+    const uint4 ta = ra[i];
+    const uint4 tb = rb[i];
+    wa[i * 4 + 0] = ta.x, wa[i * 4 + 1] = ta.y, wa[i * 4 + 2] = ta.z, wa[i * 4 + 3] = ta.w;
+    wb[i * 4 + 0] = tb.x, wb[i * 4 + 1] = tb.y, wb[i * 4 + 2] = tb.z, wb[i * 4 + 3] = tb.w;
+  }
+  __half2 acc = as_h2(0u);
+#pragma unroll
+  for (int m = 0; m < 12; m++) {
+    const __half2 even = as_h2(prmt(wa[m], wb[m], 0x5410));  // (a[2m],   b[2m])
+    const __half2 odd = as_h2(prmt(wa[m], wb[m], 0x7632));   // (a[2m+1], b[2m+1])
+    acc = __hadd2_rn(acc, __hmul2_rn(__low2half2(as_h2(q[m])), even));
+    acc = __hadd2_rn(acc, __hmul2_rn(__high2half2(as_h2(q[m])), odd));
+  }
+  return acc;
+}
+
+__global__ void __launch_bounds__(kRtThreads, 2)
+    refine_f16_tiled_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
+                            const long long *__restrict__ p1, long long *__restrict__ p1_new,
+                            int h, int w, int dilation_max) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint4 *tile = reinterpret_cast<uint4 *>(smem_raw);
+  unsigned long long *mbar = reinterpret_cast<unsigned long long *>(smem_raw + kRtTileBytes);
+  int *red = reinterpret_cast<int *>(smem_raw + kRtTileBytes + 16);  // umin, umax, vmin, vmax
+
+  constexpr int radius = 3, nside = 7;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int qx = blockIdx.x * kRtQ + (tid & (kRtQ - 1));
+  const int qy = blockIdx.y * kRtQ + (tid >> 4);
+  const int b = blockIdx.z;
+  const bool active = (qx < w) && (qy < h);
+  const size_t n = static_cast<size_t>(h) * w;
+  const size_t gi = static_cast<size_t>(b) * n + static_cast<size_t>(qy) * w + qx;
+
+  if (tid == 0) {
+    red[0] = INT_MAX, red[1] = INT_MIN, red[2] = INT_MAX, red[3] = INT_MIN;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  longlong2 p = make_longlong2(0, 0);
+  if (active) p = reinterpret_cast<const longlong2 *>(p1)[gi];
+  // candidates further than radius*(sum of dilations) ... the first level already decides:
+  // beyond radius*dilation_max of the image no candidate is ever inside it, and the centre
+  // never moves (same early-out as the direct kernel)
+  const long long reach = static_cast<long long>(radius) * dilation_max;
+  const bool live = active && !(p.x < -reach || p.x >= w + reach || p.y < -reach || p.y >= h + reach);
+  int u0 = live ? static_cast<int>(p.x) : 0, v0 = live ? static_cast<int>(p.y) : 0;
+  __syncthreads();
+  {
+    const int a0 = __reduce_min_sync(0xffffffffu, live ? u0 : INT_MAX);
+    const int a1 = __reduce_max_sync(0xffffffffu, live ? u0 : INT_MIN);
+    const int a2 = __reduce_min_sync(0xffffffffu, live ? v0 : INT_MAX);
+    const int a3 = __reduce_max_sync(0xffffffffu, live ? v0 : INT_MIN);
+    if (lane == 0 && a0 != INT_MAX) {
+      atomicMin(&red[0], a0), atomicMax(&red[1], a1), atomicMin(&red[2], a2), atomicMax(&red[3], a3);
+    }
+  }
+  __syncthreads();
+  const bool any_live = red[0] != INT_MAX;
+  // staged box [ou, ou+T) x [ov, ov+T), centred on the bounding box of the CTA's matches
+  const int ou = any_live ? ((red[0] + red[1] + 1 - kRtT) >> 1) : 0;
+  const int ov = any_live ? ((red[2] + red[3] + 1 - kRtT) >> 1) : 0;
+  const int c0 = max(ou, 0), c1 = min(ou + kRtT, w);  // columns of the box inside the image
+  const int r0 = max(ov, 0), r1 = min(ov + kRtT, h);
+  const bool have_box = any_live && c1 > c0 && r1 > r0;
+  const __half *img_h = D11 + static_cast<size_t>(b) * n * 24;
+  if (tid < 32 && have_box) {
+    const uint32_t row_bytes = static_cast<uint32_t>(c1 - c0) * 48u;
+    if (lane == 0) {
+      const uint32_t total = row_bytes * static_cast<uint32_t>(r1 - r0);
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)),
+                   "r"(total)
+                   : "memory");
+    }
+    __syncwarp();
+    for (int gv = r0 + lane; gv < r1; gv += 32) {
+      const __half *src = img_h + (static_cast<size_t>(gv) * w + c0) * 24;
+      const uint4 *dst = tile + (static_cast<size_t>(gv - ov) * kRtT + (c0 - ou)) * kRtRowU4;
+      asm volatile(
+          "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+              "r"(smem_u32(dst)),
+          "l"(src), "r"(row_bytes), "r"(smem_u32(mbar))
+          : "memory");
+    }
+  }
+  // the query descriptor streams in while the box lands
+  uint32_t q[12];
+  if (active) {
+    const uint4 *qrow = reinterpret_cast<const uint4 *>(D21 + gi * 24);
+#pragma unroll
+    for (int i = 0; i < kRtRowU4; i++) {
+      const uint4 t = __ldg(qrow + i);
+      q[i * 4 + 0] = t.x, q[i * 4 + 1] = t.y, q[i * 4 + 2] = t.z, q[i * 4 + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 12; i++) q[i] = 0u;
+  }
+  if (have_box) {
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(smem_u32(mbar)), "r"(0u)
+          : "memory");
+    }
+  }
+
+  const uint4 *img = reinterpret_cast<const uint4 *>(img_h);
+  __half max_score = __ushort_as_half(0);  // +0 (see the contract above)
+  int u_new = u0, v_new = v0;
+  for (int d = dilation_max; d > 0; d--) {
+    const int rd = radius * d;
+    const bool inside = have_box && (u0 - rd >= ou) && (u0 + rd < ou + kRtT) && (v0 - rd >= ov) &&
+                        (v0 + rd < ov + kRtT) && (6 * d < kRtT);
+    if (!__any_sync(0xffffffffu, live)) break;  // nothing to do in this warp (no barriers below)
+    if (__all_sync(0xffffffffu, inside || !live)) {
+      // ---- whole warp inside the staged box: unrolled, unchecked loads from shared memory
+      // (at least one live lane is inside, hence 6*d < T and dead lanes stay addressable too)
+      unsigned umask = 0, vmask = 0;  // which of the 7 columns / rows are inside the image
+      if (live) {
+#pragma unroll
+        for (int i = 0; i < nside; i++) {
+          const int uu = u0 - rd + i * d, vv = v0 - rd + i * d;
+          umask |= (uu >= 0 && uu < w) ? (1u << i) : 0u;
+          vmask |= (vv >= 0 && vv < h) ? (1u << i) : 0u;
+        }
+      }
+      // dead lanes read the box corner (always addressable: 6*d < T) and are masked
+      const int bu = live ? (u0 - rd - ou) : 0, bv = live ? (v0 - rd - ov) : 0;
+      const uint4 *base = tile + (bv * kRtT + bu) * kRtRowU4;
+      const int du4 = d * kRtRowU4, dv4 = d * kRtT * kRtRowU4;
+      int best = -1;
+#pragma unroll
+      for (int c = 0; c < nside * nside; c += 2) {
+        const int ia = c / nside, ja = c % nside;
+        const int cb = (c + 1 < nside * nside) ? c + 1 : c;  // the last pair repeats the row
+        const int ib = cb / nside, jb = cb % nside;
+        const __half2 acc = score_pair(base + ia * du4 + ja * dv4, base + ib * du4 + jb * dv4, q);
+        const bool oka = ((umask >> ia) & (vmask >> ja) & 1u) != 0;
+        const bool okb = (c + 1 < nside * nside) && (((umask >> ib) & (vmask >> jb) & 1u) != 0);
+        const __half sa = __low2half(acc), sb = __high2half(acc);
+        if (oka && __hgt(sa, max_score)) max_score = sa, best = c;
+        if (okb && __hgt(sb, max_score)) max_score = sb, best = c + 1;
+      }
+      if (best >= 0) {
+        const int bi = best / nside, bj = best - bi * nside;
+        u_new = u0 - rd + bi * d;
+        v_new = v0 - rd + bj * d;
+      }
+    } else if (live) {
+      // ---- checked path from global memory (a window leaves the box)
+      for (int c = 0; c < nside * nside; c += 2) {
+        const int ia = c / nside, ja = c - ia * nside;
+        int ib = ia, jb = ja + 1;
+        if (jb == nside) jb = 0, ib = ia + 1;
+        const int ua = u0 - rd + ia * d, va = v0 - rd + ja * d;
+        const int ub = u0 - rd + ib * d, vb = v0 - rd + jb * d;
+        const bool ina = (va >= 0) & (va < h) & (ua >= 0) & (ua < w);
+        const bool inb = (c + 1 < nside * nside) & (vb >= 0) & (vb < h) & (ub >= 0) & (ub < w);
+        if (!(ina | inb)) continue;
+        const int uac = min(max(ua, 0), w - 1), vac = min(max(va, 0), h - 1);
+        const int ubc = min(max(ub, 0), w - 1), vbc = min(max(vb, 0), h - 1);
+        const __half2 acc = score_pair(img + (static_cast<size_t>(vac) * w + uac) * kRtRowU4,
+                                       img + (static_cast<size_t>(vbc) * w + ubc) * kRtRowU4, q);
+        const __half sa = __low2half(acc), sb = __high2half(acc);
+        if (ina && __hgt(sa, max_score)) max_score = sa, u_new = ua, v_new = va;
+        if (inb && __hgt(sb, max_score)) max_score = sb, u_new = ub, v_new = vb;
+      }
+    }
+    u0 = u_new;  // recentre for the next dilation level (:75-76)
+    v0 = v_new;
+  }
+  if (active) {
+    reinterpret_cast<longlong2 *>(p1_new)[gi] =
+        live ? make_longlong2(static_cast<long long>(u_new), static_cast<long long>(v_new)) : p;
+  }
+}
+
 // Generic path: any fdim, any of the three dtypes; accumulation in T as the reference does.
 template <typename T>
 struct RefineOps;
@@ -456,14 +631,14 @@ extern "C" int m3r_iter_proj_v(const float *rays, const float *pts, const float 
   M3R_REQUIRE(b <= 65535, "iter_proj: batch %d exceeds grid.y limit", b);
   M3R_REQUIRE((reinterpret_cast<uintptr_t>(p_new) & 7u) == 0, "iter_proj: p_new not 8-byte aligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const dim3 block(kIpWarps * 32);
+  const dim3 block(kIpThreads);
   const dim3 grid((n + block.x - 1) / block.x, b);
   if (variant == 1) {
-    iter_proj_kernel<false><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
-                                                   max_iter, lambda_init, cost_thresh);
-  } else if (variant == 0 || variant == 2) {
-    iter_proj_kernel<true><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
-                                                  max_iter, lambda_init, cost_thresh);
+    iter_proj_kernel<1><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
+                                               max_iter, lambda_init, cost_thresh);
+  } else if (variant == 0) {
+    iter_proj_kernel<0><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
+                                               max_iter, lambda_init, cost_thresh);
   } else {
     set_error("iter_proj: unknown variant %d", variant);
     return M3R_ERR_INVALID_ARGUMENT;
@@ -500,7 +675,21 @@ extern "C" int m3r_refine_matches_v(const void *D11, const void *D21, const int6
   long long *p1nl = reinterpret_cast<long long *>(p1_new);
   if (dtype == M3R_DTYPE_F16) {
     const bool fast = (fdim == 24) && aligned16(D11) && aligned16(D21) && variant != 1;
-    if (fast) {
+    const bool tiled = fast && variant == 0 && radius == 3 && dilation_max >= 1 &&
+                       static_cast<long long>(n) == static_cast<long long>(h) * w;
+    if (tiled) {
+      static bool attr_set = false;  // benign race: idempotent
+      if (!attr_set) {
+        M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
+        attr_set = true;
+      }
+      const dim3 tgrid((w + kRtQ - 1) / kRtQ, (h + kRtQ - 1) / kRtQ, b);
+      M3R_REQUIRE(tgrid.y <= 65535, "refine_matches: image too tall");
+      refine_f16_tiled_kernel<<<tgrid, kRtThreads, kRtSmemBytes, s>>>(
+          static_cast<const __half *>(D11), static_cast<const __half *>(D21), p1l, p1nl, h, w,
+          dilation_max);
+    } else if (fast) {
       refine_f16_kernel<24><<<grid, block, 0, s>>>(static_cast<const __half *>(D11),
                                                    static_cast<const __half *>(D21), p1l, p1nl,
                                                    h, w, n, radius, dilation_max);

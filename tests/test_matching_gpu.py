@@ -53,10 +53,10 @@ def test_iter_proj_vs_oracle(backends, oracle, h, w, b, seed, init):
 
 @pytest.mark.parametrize("init", ["identity", "random"])
 def test_iter_proj_variants_bit_identical(backends, init):
-    """The warp-staged kernel and the direct-gather kernel compute the same bits."""
+    """The memoised kernel and the re-evaluating kernel compute the same bits."""
     m, rays, pts, p0 = _inputs(120, 168, 2, 7, init)
     a = backends.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6, _variant=1)
-    c = backends.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6, _variant=2)
+    c = backends.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6, _variant=0)
     assert torch.equal(a[0], c[0]) and torch.equal(a[1], c[1])
 
 
@@ -112,13 +112,33 @@ def test_refine_bit_exact_vs_oracle(backends, oracle, dtype, h, w, b, fdim, radi
     assert out.dtype == torch.int64 and torch.equal(out.cpu(), ref)
 
 
-def test_refine_fast_and_generic_kernels_agree(backends):
-    m = synth.make_match_inputs(96, 128, seed=12, device="cuda")
-    D11, D21 = m["D11"].half(), m["D21"].view(1, -1, 24).half()
-    p1 = _p1(96, 128, 1, 96 * 128, 2)
-    (a,) = backends.refine_matches(D11, D21, p1, 3, 5, _variant=0)
-    (c,) = backends.refine_matches(D11, D21, p1, 3, 5, _variant=1)
-    assert torch.equal(a, c)
+@pytest.mark.parametrize("h,w,b,kind", [(96, 128, 1, "random"), (96, 128, 2, "smooth"), (77, 101, 1, "smooth"),
+                                        (384, 512, 1, "smooth"), (50, 70, 1, "jumpy"), (16, 16, 1, "smooth")])
+def test_refine_kernels_agree(backends, oracle, h, w, b, kind):
+    """Tiled (TMA-staged shared-memory box), direct-pair and generic kernels: same bits.
+    `smooth` keeps every window inside the staged box (unrolled shared-memory path, image
+    borders masked); `jumpy` and `random` push windows out of the box (checked global path)."""
+    m = synth.make_match_inputs(h, w, b=b, seed=12, device="cuda")
+    D11, D21 = m["D11"].half(), m["D21"].view(b, -1, 24).half()
+    if kind == "random":
+        p1 = _p1(h, w, b, h * w, 2, spread=4)
+    else:
+        p1 = m["true_uv"].round().long().clone()
+        g = torch.Generator().manual_seed(5)
+        p1 += torch.randint(-2, 3, p1.shape, generator=g).cuda()
+        if kind == "jumpy":  # a tenth of the matches are far from their neighbours'
+            sel = (torch.rand(p1.shape[:2], generator=g) < 0.1).cuda()
+            p1[sel] += torch.tensor([23, -19], device="cuda")
+    p1 = p1.contiguous()
+    outs = [backends.refine_matches(D11, D21, p1, 3, 5, _variant=v)[0] for v in (0, 1, 2)]
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    if h * w <= 128 * 128:
+        (ref,) = oracle.refine_matches(D11, D21, p1, 3, 5)
+        assert torch.equal(outs[0].cpu(), ref)
+    for dil in (1, 2, 7, 9):  # 9: windows wider than the staged box
+        a = backends.refine_matches(D11, D21, p1, 3, dil, _variant=0)[0]
+        c = backends.refine_matches(D11, D21, p1, 3, dil, _variant=1)[0]
+        assert torch.equal(a, c), f"dilation_max={dil}"
 
 
 def test_refine_edge_cases(backends, oracle):
