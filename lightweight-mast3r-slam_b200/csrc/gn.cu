@@ -88,10 +88,27 @@ __device__ __forceinline__ void act_sim3(const Pose &T, const float X[3], float 
   Y[2] = Y[2] * T.s + T.t[2];
 }
 
+// single-MUFU approximations (<= 2 ulp): the streaming kernel is instruction-issue bound and
+// the 1e-4 pose tolerance leaves five orders of magnitude of head-room
+__device__ __forceinline__ float rsqrt_fast(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sqrt_fast(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_fast(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float huber_w(float r) {
-  // gn_kernels.cu:172-175 (k = 1.345)
-  const float a = fabsf(r);
-  return a < 1.345f ? 1.0f : __fdividef(1.345f, a);
+  // gn_kernels.cu:172-175 (k = 1.345): 1 if |r| < k else k/|r|  ==  min(1, k/|r|)
+  return fminf(1.0f, 1.345f * rcp_fast(fabsf(r)));
 }
 
 // ----------------------------------------------------------------------------------------
@@ -137,21 +154,21 @@ template <>
 struct Residual<M3R_GN_RAYS> {
   static __device__ __forceinline__ void point(const GnParams &P, const Pose &Tij,
                                                const float Xi[3], const float Xj[3], float q,
-                                               long long, float acc[kNAcc]) {
+                                               int, float acc[kNAcc]) {
     const float n2i = Xi[0] * Xi[0] + Xi[1] * Xi[1] + Xi[2] * Xi[2];
-    const float n1i = sqrtf(n2i);
-    const float n1i_inv = __frcp_rn(n1i);
+    const float n1i_inv = rsqrt_fast(n2i);
+    const float n1i = n2i * n1i_inv;
     float Pj[3];
     act_sim3(Tij, Xj, Pj);
     const float n2j = Pj[0] * Pj[0] + Pj[1] * Pj[1] + Pj[2] * Pj[2];
-    const float n1j = sqrtf(n2j);
-    const float n1j_inv = __frcp_rn(n1j);
+    const float n1j_inv = rsqrt_fast(n2j);
+    const float n1j = n2j * n1j_inv;
     const float r[3] = {n1j_inv * Pj[0], n1j_inv * Pj[1], n1j_inv * Pj[2]};
     const float e0 = r[0] - n1i_inv * Xi[0];
     const float e1 = r[1] - n1i_inv * Xi[1];
     const float e2 = r[2] - n1i_inv * Xi[2];
     const float e3 = n1j - n1i;
-    const float sq = sqrtf(q);
+    const float sq = sqrt_fast(q);
     const float swr = P.sigma_a_inv * sq;
     const float swd = P.sigma_b_inv * sq;
     const float wr = swr * swr, wd = swd * swd;
@@ -159,7 +176,7 @@ struct Residual<M3R_GN_RAYS> {
     const float w1 = huber_w(swr * e1) * wr;
     const float w2 = huber_w(swr * e2) * wr;
     const float w3 = huber_w(swd * e3) * wd;
-    const float n3 = __fdividef(n1j_inv, n2j);  // 1/|P|^3 (:982)
+    const float n3 = n1j_inv * n1j_inv * n1j_inv;  // 1/|P|^3 (:982)
     const float axx = n1j_inv - Pj[0] * Pj[0] * n3;
     const float ayy = n1j_inv - Pj[1] * Pj[1] * n3;
     const float azz = n1j_inv - Pj[2] * Pj[2] * n3;
@@ -194,11 +211,11 @@ template <>
 struct Residual<M3R_GN_POINTS> {
   static __device__ __forceinline__ void point(const GnParams &P, const Pose &Tij,
                                                const float Xi[3], const float Xj[3], float q,
-                                               long long, float acc[kNAcc]) {
+                                               int, float acc[kNAcc]) {
     float Pj[3];
     act_sim3(Tij, Xj, Pj);
     const float e0 = Pj[0] - Xi[0], e1 = Pj[1] - Xi[1], e2 = Pj[2] - Xi[2];
-    const float sw = P.sigma_a_inv * sqrtf(q);
+    const float sw = P.sigma_a_inv * sqrt_fast(q);
     const float wc = sw * sw;
     const float w0 = huber_w(sw * e0) * wc;
     const float w1 = huber_w(sw * e1) * wc;
@@ -223,23 +240,23 @@ template <>
 struct Residual<M3R_GN_CALIB> {
   static __device__ __forceinline__ void point(const GnParams &P, const Pose &Tij,
                                                const float Xi[3], const float Xj[3], float q,
-                                               long long ind_Xi, float acc[kNAcc]) {
+                                               int ind_Xi, float acc[kNAcc]) {
     float Pj[3];
     act_sim3(Tij, Xj, Pj);
     const bool valid_z = (Pj[2] > P.z_eps) && (Xi[2] > P.z_eps);  // :1368
     if (!valid_z) return;
-    const float iz = __frcp_rn(Pj[2]);
+    const float iz = rcp_fast(Pj[2]);
     const float x = Pj[0] * iz, y = Pj[1] * iz;
     const float u = P.fx * x + P.cx;
     const float v = P.fy * y + P.cy;
     const bool valid_uv = (u > P.u_lo) && (u < P.u_hi) && (v > P.v_lo) && (v < P.v_hi);  // :1382-1383
     if (!valid_uv) return;
-    const int u_t = static_cast<int>(ind_Xi % P.width);  // :1361-1362
-    const int v_t = static_cast<int>(ind_Xi / P.width);
+    const int v_t = ind_Xi / P.width;  // :1361-1362
+    const int u_t = ind_Xi - v_t * P.width;
     const float e0 = u - static_cast<float>(u_t);
     const float e1 = v - static_cast<float>(v_t);
-    const float e2 = logf(Pj[2]) - logf(Xi[2]);
-    const float sq = sqrtf(q);
+    const float e2 = __logf(Pj[2] * rcp_fast(Xi[2]));  // log z_j->i - log z_i
+    const float sq = sqrt_fast(q);
     const float swp = P.sigma_a_inv * sq;
     const float swd = P.sigma_b_inv * sq;
     const float wp = swp * swp, wd = swd * swd;
@@ -264,123 +281,213 @@ struct Residual<M3R_GN_CALIB> {
 };
 
 // ----------------------------------------------------------------------------------------
-// accumulation kernel
+// per-call preparation (m3r_gn_begin): packed keyframes and compacted match lists
 // ----------------------------------------------------------------------------------------
+// Xs, Cs, idx_ii2jj, valid_match and Q do not change over the iterations of one call, and
+// neither does the part of the validity test that depends only on them
+// (valid_match & q > Q_thresh & c_i > C_thresh & c_j > C_thresh, gn_kernels.cu:914-951).
+// So the call first
+//   * packs every keyframe point as one 16-byte (x, y, z, c) record: the per-iteration gathers
+//     become single aligned 128-bit loads instead of 3+1 scalar ones;
+//   * compacts, per (edge, 1024-point segment), the points that pass the test into a dense
+//     list of (k, idx, q): the per-iteration kernel then runs with all 32 lanes of a warp on
+//     contributing points (a quarter of the lanes idled on invalid points before), reads 12
+//     bytes per surviving point instead of 13 per point, and carries no validity logic.
+// Order within a segment is preserved and segments are summed in a fixed order, so results
+// stay bitwise reproducible.
 constexpr int kAccThreads = 256;
 constexpr int kAccWarps = kAccThreads / 32;
-constexpr int kChunk = 8192;  // points per work item (multiple of 4*kAccThreads)
+constexpr int kSeg = 1024;                  // points per warp segment
+constexpr int kChunk = kSeg * kAccWarps;    // points per work item (one CTA pass)
 
-struct AccArgs {
-  const float *Twc;
-  const float *Xs;
-  const float *Cs;
-  const long long *idx;        // shard rows
+__global__ void __launch_bounds__(256)
+    gn_pack_kernel(const float *__restrict__ Xs, const float *__restrict__ Cs,
+                   float4 *__restrict__ P, size_t total) {
+  for (size_t k = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < total;
+       k += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    P[k] = make_float4(__ldcs(Xs + 3 * k), __ldcs(Xs + 3 * k + 1), __ldcs(Xs + 3 * k + 2),
+                       __ldcs(Cs + k));
+  }
+}
+
+struct CompactArgs {
+  const float *Cs;             // [N, n]
+  const long long *idx;        // shard rows [ES, n]
   const unsigned char *valid;  // shard rows
   const float *Q;              // shard rows
+  const int *pose_i, *pose_j;  // [E] whole graph
+  int *ck, *cidx;              // [ES * chunks * kChunk]
+  float *cq;
+  int *counts;                 // [ES * chunks * kAccWarps]
+  int n, edge_begin, num_shard_edges, chunks_per_edge;
+  float C_thresh, Q_thresh;
+};
+
+__global__ void __launch_bounds__(kAccThreads) gn_compact_kernel(const CompactArgs A) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n = A.n;
+  const int items = A.num_shard_edges * A.chunks_per_edge;
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int le = item / A.chunks_per_edge;
+    const int ch = item - le * A.chunks_per_edge;
+    const int e = A.edge_begin + le;
+    const float *Ci = A.Cs + static_cast<size_t>(A.pose_i[e]) * n;
+    const float *Cj = A.Cs + static_cast<size_t>(A.pose_j[e]) * n;
+    const long long *idx_e = A.idx + static_cast<size_t>(le) * n;
+    const unsigned char *val_e = A.valid + static_cast<size_t>(le) * n;
+    const float *Q_e = A.Q + static_cast<size_t>(le) * n;
+    const size_t slot = (static_cast<size_t>(item) * kAccWarps + warp) * kSeg;
+    const int k_begin = ch * kChunk + warp * kSeg;
+    int fill = 0;
+    constexpr int U = 4;  // rounds in flight: the kernel is a latency-bound stream + gather
+    for (int r0 = 0; r0 < kSeg / 32; r0 += U) {
+      float q[U], cj[U];
+      long long raw[U];
+      unsigned char vm[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int k = k_begin + (r0 + u) * 32 + lane;
+        const bool in = k < n;
+        q[u] = in ? __ldcs(Q_e + k) : 0.f;
+        raw[u] = in ? __ldcs(idx_e + k) : 0LL;
+        vm[u] = in ? __ldcs(val_e + k) : static_cast<unsigned char>(0);
+        cj[u] = in ? __ldg(Cj + k) : 0.f;
+      }
+      bool ok[U];
+      int id[U];
+      float ci[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        ok[u] = (vm[u] != 0) && (q[u] > A.Q_thresh) && (cj[u] > A.C_thresh);
+        // clamp keeps a corrupt index from reading outside keyframe i's pointmap
+        id[u] = ok[u] ? static_cast<int>(min(max(raw[u], 0LL), static_cast<long long>(n - 1))) : 0;
+        ci[u] = ok[u] ? __ldg(Ci + id[u]) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const bool keep = ok[u] && (ci[u] > A.C_thresh);
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+          const size_t pos = slot + fill + __popc(m & ((1u << lane) - 1u));
+          A.ck[pos] = k_begin + (r0 + u) * 32 + lane;
+          A.cidx[pos] = id[u];
+          A.cq[pos] = q[u];
+        }
+        fill += __popc(m);
+      }
+    }
+    if (lane == 0) A.counts[item * kAccWarps + warp] = fill;
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// accumulation kernel (every iteration)
+// ----------------------------------------------------------------------------------------
+struct AccArgs {
+  const float *Twc;
+  const float4 *P;
+  const int *ck, *cidx;
+  const float *cq;
+  const int *counts;
   const int *pose_i;           // [E] whole graph, packed pose index
   const int *pose_j;
   const float *K;              // calib
   double *partials;            // [items, 35]
   const int *flags;
   int n, edge_begin, num_shard_edges, chunks_per_edge;
-  GnParams P;
+  GnParams P_;
 };
 
-__device__ __forceinline__ float4 ldcs4(const float *p) {
-  return __ldcs(reinterpret_cast<const float4 *>(p));
+// Latency is hidden with per-warp cp.async rings in shared memory rather than with registers
+// (the 35 accumulators leave no room for a deep register pipeline, and a one-round register
+// pipeline left the warps waiting on the gathers: ncu source view, profiles/).  Per round of 32
+// list entries a warp commits one group holding
+//   * the (k, idx, q) entries of round r+6  (three 128-byte rows, 24 lanes x 16 B), and
+//   * the two 16-byte point records of round r+3 for every lane (gathers),
+// and waits until at most two groups are pending, i.e. until the group of round r-3 has landed:
+// the records of round r and the entries needed to issue the gathers of round r+3.
+constexpr int kEntSlots = 8;  // entry ring (rounds r .. r+6 are live)
+constexpr int kRecSlots = 4;  // record ring (rounds r .. r+3)
+constexpr int kGatherLead = 3, kEntryLead = 6;
+struct __align__(16) AccWarpSmem {
+  int ent[kEntSlots][3][32];     // [slot][k | idx | q bits][lane]
+  float4 rec[kRecSlots][2][32];  // [slot][Xj | Xi][lane]
+};
+constexpr int kAccSmemBytes = kAccWarps * static_cast<int>(sizeof(AccWarpSmem));
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+               "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async16_ca(void *smem_dst, const void *gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+               "l"(gsrc)
+               : "memory");
 }
 
-template <int KIND, int VEC>
+template <int KIND>
 __global__ void __launch_bounds__(kAccThreads, 2) gn_accumulate_kernel(const AccArgs A) {
   if (A.flags[0]) return;  // converged earlier: nothing to do
+  extern __shared__ __align__(16) unsigned char acc_smem_raw[];
   __shared__ double red[kAccWarps][kNAcc];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  AccWarpSmem &W = reinterpret_cast<AccWarpSmem *>(acc_smem_raw)[warp];
   const int n = A.n;
   const int items = A.num_shard_edges * A.chunks_per_edge;
 
-  GnParams P = A.P;
+  GnParams P = A.P_;
   if (KIND == M3R_GN_CALIB) {  // intrinsics live on the device (gn_kernels.cu:1274-1279)
     P.fx = __ldg(A.K + 0), P.fy = __ldg(A.K + 4), P.cx = __ldg(A.K + 2), P.cy = __ldg(A.K + 5);
   }
 
   for (int item = blockIdx.x; item < items; item += gridDim.x) {
     const int le = item / A.chunks_per_edge;  // edge within the shard
-    const int ch = item - le * A.chunks_per_edge;
     const int e = A.edge_begin + le;
     const int ix = A.pose_i[e], jx = A.pose_j[e];
-    const Pose Ti = load_pose(A.Twc, ix);
-    const Pose Tj = load_pose(A.Twc, jx);
-    const Pose Tij = rel_sim3(Ti, Tj);
-
-    const float *Xi_base = A.Xs + static_cast<size_t>(ix) * n * 3;
-    const float *Xj_base = A.Xs + static_cast<size_t>(jx) * n * 3;
-    const float *Ci_base = A.Cs + static_cast<size_t>(ix) * n;
-    const float *Cj_base = A.Cs + static_cast<size_t>(jx) * n;
-    const long long *idx_e = A.idx + static_cast<size_t>(le) * n;
-    const unsigned char *val_e = A.valid + static_cast<size_t>(le) * n;
-    const float *Q_e = A.Q + static_cast<size_t>(le) * n;
+    const Pose Tij = rel_sim3(load_pose(A.Twc, ix), load_pose(A.Twc, jx));
+    const float4 *Pi = A.P + static_cast<size_t>(ix) * n;
+    const float4 *Pj = A.P + static_cast<size_t>(jx) * n;
+    const size_t slot = (static_cast<size_t>(item) * kAccWarps + warp) * kSeg;
+    const int cnt = A.counts[item * kAccWarps + warp];
+    const int nr = (cnt + 31) >> 5;
+    // lanes 0-7 copy the k row of a round, 8-15 the idx row, 16-23 the q row (16 B each)
+    const int erow = lane >> 3;
+    const int *esrc = (erow == 0 ? A.ck : erow == 1 ? A.cidx : reinterpret_cast<const int *>(A.cq)) +
+                      slot + (lane & 7) * 4;
 
     float acc[kNAcc];
 #pragma unroll
     for (int k = 0; k < kNAcc; k++) acc[k] = 0.f;
 
-    const int k_begin = ch * kChunk;
-    const int k_end = min(n, k_begin + kChunk);
-    for (int k0 = k_begin + threadIdx.x * VEC; k0 < k_end; k0 += kAccThreads * VEC) {
-      float Xj[VEC][3], qv[VEC], cj[VEC];
-      long long id[VEC];
-      unsigned char vm[VEC];
-      if (VEC == 4) {
-        const float4 a = __ldg(reinterpret_cast<const float4 *>(Xj_base + static_cast<size_t>(k0) * 3));
-        const float4 b = __ldg(reinterpret_cast<const float4 *>(Xj_base + static_cast<size_t>(k0) * 3 + 4));
-        const float4 c = __ldg(reinterpret_cast<const float4 *>(Xj_base + static_cast<size_t>(k0) * 3 + 8));
-        Xj[0][0] = a.x, Xj[0][1] = a.y, Xj[0][2] = a.z;
-        Xj[1 % VEC][0] = a.w, Xj[1 % VEC][1] = b.x, Xj[1 % VEC][2] = b.y;
-        Xj[2 % VEC][0] = b.z, Xj[2 % VEC][1] = b.w, Xj[2 % VEC][2] = c.x;
-        Xj[3 % VEC][0] = c.y, Xj[3 % VEC][1] = c.z, Xj[3 % VEC][2] = c.w;
-        const float4 qq = ldcs4(Q_e + k0);
-        qv[0] = qq.x, qv[1 % VEC] = qq.y, qv[2 % VEC] = qq.z, qv[3 % VEC] = qq.w;
-        const float4 cc = __ldg(reinterpret_cast<const float4 *>(Cj_base + k0));
-        cj[0] = cc.x, cj[1 % VEC] = cc.y, cj[2 % VEC] = cc.z, cj[3 % VEC] = cc.w;
-        const longlong2 i0 = __ldcs(reinterpret_cast<const longlong2 *>(idx_e + k0));
-        const longlong2 i1 = __ldcs(reinterpret_cast<const longlong2 *>(idx_e + k0 + 2));
-        id[0] = i0.x, id[1 % VEC] = i0.y, id[2 % VEC] = i1.x, id[3 % VEC] = i1.y;
-        const uchar4 vv = __ldcs(reinterpret_cast<const uchar4 *>(val_e + k0));
-        vm[0] = vv.x, vm[1 % VEC] = vv.y, vm[2 % VEC] = vv.z, vm[3 % VEC] = vv.w;
-      } else {
-#pragma unroll
-        for (int p = 0; p < VEC; p++) {
-          const int k = k0 + p;
-          Xj[p][0] = __ldg(Xj_base + static_cast<size_t>(k) * 3 + 0);
-          Xj[p][1] = __ldg(Xj_base + static_cast<size_t>(k) * 3 + 1);
-          Xj[p][2] = __ldg(Xj_base + static_cast<size_t>(k) * 3 + 2);
-          qv[p] = __ldcs(Q_e + k);
-          cj[p] = __ldg(Cj_base + k);
-          id[p] = __ldcs(idx_e + k);
-          vm[p] = __ldcs(val_e + k);
-        }
+    for (int t = -kEntryLead; t < nr; t++) {
+      asm volatile("cp.async.wait_group %0;" ::"n"(kGatherLead - 1) : "memory");
+      __syncwarp();
+      if (t + kEntryLead < nr && lane < 24) {
+        cp_async16(&W.ent[(t + kEntryLead) & (kEntSlots - 1)][erow][(lane & 7) * 4],
+                   esrc + (t + kEntryLead) * 32);
       }
-      // gathers from keyframe i (:914-918, :951): invalid matches read point 0, as the
-      // reference does, but the loads are only issued for points that can contribute
-      float Xi[VEC][3], ci[VEC];
-      bool ok[VEC];
-#pragma unroll
-      for (int p = 0; p < VEC; p++) {
-        ok[p] = (vm[p] != 0) && (qv[p] > P.Q_thresh) && (cj[p] > P.C_thresh);
-        // clamp keeps a corrupt index from reading outside keyframe i's pointmap
-        const long long ii = ok[p] ? min(max(id[p], 0LL), static_cast<long long>(n - 1)) : 0LL;
-        id[p] = ii;
-        Xi[p][0] = __ldg(Xi_base + ii * 3 + 0);
-        Xi[p][1] = __ldg(Xi_base + ii * 3 + 1);
-        Xi[p][2] = __ldg(Xi_base + ii * 3 + 2);
-        ci[p] = __ldg(Ci_base + ii);
+      const int tg = t + kGatherLead;
+      if (tg >= 0 && tg < nr) {
+        const bool in = tg * 32 + lane < cnt;
+        const int kk = in ? W.ent[tg & (kEntSlots - 1)][0][lane] : 0;
+        const int ii = in ? W.ent[tg & (kEntSlots - 1)][1][lane] : 0;
+        cp_async16_ca(&W.rec[tg & (kRecSlots - 1)][0][lane], Pj + kk);
+        cp_async16_ca(&W.rec[tg & (kRecSlots - 1)][1][lane], Pi + ii);
       }
-#pragma unroll
-      for (int p = 0; p < VEC; p++) {
-        if (ok[p] && ci[p] > P.C_thresh)
-          Residual<KIND>::point(P, Tij, Xi[p], Xj[p], qv[p], id[p], acc);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      if (t >= 0 && t * 32 + lane < cnt) {
+        const float4 xj = W.rec[t & (kRecSlots - 1)][0][lane];
+        const float4 xi = W.rec[t & (kRecSlots - 1)][1][lane];
+        const int i1 = W.ent[t & (kEntSlots - 1)][1][lane];
+        const float q1 = __int_as_float(W.ent[t & (kEntSlots - 1)][2][lane]);
+        const float Xi[3] = {xi.x, xi.y, xi.z}, Xj[3] = {xj.x, xj.y, xj.z};
+        Residual<KIND>::point(P, Tij, Xi, Xj, q1, i1, acc);
       }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
 
     // warp tree in fp32, then fp64 across warps in a fixed order
 #pragma unroll
@@ -943,6 +1050,10 @@ struct m3r_gn_workspace {
   int device = 0;
   DevBuf<int> pose_i, pose_j;     // [E] packed pose index per directed edge
   DevBuf<unsigned char> first;    // [2E] scratch of the id remap
+  DevBuf<float4> packed;          // [N, n] (x, y, z, c) records of every keyframe point
+  DevBuf<int> ck, cidx;           // [items * kChunk] compacted match lists (point k, match idx)
+  DevBuf<float> cq;               //                  and their confidences
+  DevBuf<int> counts;             // [items * kAccWarps] entries per warp segment
   DevBuf<double> partials;        // [items, 35]
   DevBuf<double> edge_H, edge_g;  // [E_shard, 49], [E_shard, 7]
   DevBuf<double> system;          // D*D + D (single-GPU entry points)
@@ -950,6 +1061,7 @@ struct m3r_gn_workspace {
   DevBuf<double> xbuf;            // [D]
   int *flags = nullptr;           // [0] done, [1] iterations, [2] factorisation failed
   int begun_edges = -1;
+  int begun_shard_begin = -1, begun_shard_end = -1, begun_points = -1;
 };
 
 extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
@@ -969,6 +1081,7 @@ extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
 extern "C" void m3r_gn_workspace_destroy(m3r_gn_workspace *ws) {
   if (!ws) return;
   ws->pose_i.release(), ws->pose_j.release(), ws->first.release(), ws->partials.release();
+  ws->packed.release(), ws->ck.release(), ws->cidx.release(), ws->cq.release(), ws->counts.release();
   ws->edge_H.release(), ws->edge_g.release(), ws->system.release(), ws->ldiag.release();
   ws->xbuf.release();
   cudaFree(ws->flags);
@@ -1023,6 +1136,43 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
       reinterpret_cast<const long long *>(prob->ii), reinterpret_cast<const long long *>(prob->jj), E,
       ws->first.p, prob->num_poses, ws->pose_i.p, ws->pose_j.p, ws->flags);
   M3R_LAUNCH_CHECK("gn_rank_kernel");
+
+  // per-call preparation: packed keyframes, compacted match lists of this shard
+  const int n = prob->num_points;
+  const int ES = prob->edge_end - prob->edge_begin;
+  const int chunks = (n + kChunk - 1) / kChunk;
+  const size_t items = static_cast<size_t>(ES) * chunks;
+  M3R_REQUIRE(items * kAccWarps < (1ull << 31), "gn_begin: shard too large (%zu items)", items);
+  const size_t total = static_cast<size_t>(prob->num_poses) * n;
+  if ((rc = ws->packed.reserve(total))) return rc;
+  if ((rc = ws->ck.reserve(items * kChunk + 1))) return rc;
+  if ((rc = ws->cidx.reserve(items * kChunk + 1))) return rc;
+  if ((rc = ws->cq.reserve(items * kChunk + 1))) return rc;
+  if ((rc = ws->counts.reserve(items * kAccWarps + 1))) return rc;
+  {
+    const size_t want_blocks = (total + 255) / 256;
+    const size_t cap = static_cast<size_t>(kNumSMs) * 16;
+    gn_pack_kernel<<<static_cast<int>(want_blocks < cap ? want_blocks : cap), 256, 0, s>>>(
+        prob->Xs, prob->Cs, ws->packed.p, total);
+    M3R_LAUNCH_CHECK("gn_pack_kernel");
+  }
+  if (items > 0) {
+    CompactArgs c{};
+    c.Cs = prob->Cs;
+    c.idx = reinterpret_cast<const long long *>(prob->idx_ii2jj);
+    c.valid = prob->valid_match;
+    c.Q = prob->Q;
+    c.pose_i = ws->pose_i.p, c.pose_j = ws->pose_j.p;
+    c.ck = ws->ck.p, c.cidx = ws->cidx.p, c.cq = ws->cq.p, c.counts = ws->counts.p;
+    c.n = n, c.edge_begin = prob->edge_begin, c.num_shard_edges = ES, c.chunks_per_edge = chunks;
+    c.C_thresh = prob->C_thresh, c.Q_thresh = prob->Q_thresh;
+    const size_t cap = static_cast<size_t>(kNumSMs) * 8;
+    gn_compact_kernel<<<static_cast<int>(items < cap ? items : cap), kAccThreads, 0, s>>>(c);
+    M3R_LAUNCH_CHECK("gn_compact_kernel");
+  }
+  ws->begun_shard_begin = prob->edge_begin;
+  ws->begun_shard_end = prob->edge_end;
+  ws->begun_points = n;
   return M3R_OK;
 }
 
@@ -1050,12 +1200,6 @@ static GnParams make_params(const m3r_gn_problem *p) {
   return P;
 }
 
-template <int KIND>
-static void launch_accumulate(const AccArgs &a, bool vec4, int grid, cudaStream_t s) {
-  if (vec4) gn_accumulate_kernel<KIND, 4><<<grid, kAccThreads, 0, s>>>(a);
-  else gn_accumulate_kernel<KIND, 1><<<grid, kAccThreads, 0, s>>>(a);
-}
-
 extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob, double *system,
                                 void *stream) {
   M3R_REQUIRE(ws != nullptr && system != nullptr, "gn_linearize: null workspace/system");
@@ -1071,26 +1215,38 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
   if ((rc = ws->edge_H.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 49))) return rc;
   if ((rc = ws->edge_g.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 7))) return rc;
 
+  M3R_REQUIRE(prob->edge_begin == ws->begun_shard_begin && prob->edge_end == ws->begun_shard_end &&
+                  n == ws->begun_points,
+              "gn_linearize: shard differs from the one given to m3r_gn_begin");
   if (ES > 0) {
     AccArgs a{};
-    a.Twc = prob->Twc, a.Xs = prob->Xs, a.Cs = prob->Cs;
-    a.idx = reinterpret_cast<const long long *>(prob->idx_ii2jj);
-    a.valid = prob->valid_match;
-    a.Q = prob->Q;
+    a.Twc = prob->Twc;
+    a.P = ws->packed.p;
+    a.ck = ws->ck.p, a.cidx = ws->cidx.p, a.cq = ws->cq.p, a.counts = ws->counts.p;
     a.pose_i = ws->pose_i.p, a.pose_j = ws->pose_j.p;
     a.K = prob->K;
     a.partials = ws->partials.p;
     a.flags = ws->flags;
     a.n = n, a.edge_begin = prob->edge_begin, a.num_shard_edges = ES, a.chunks_per_edge = chunks;
-    a.P = make_params(prob);
-    const bool vec4 = (n % 4 == 0) && aligned16(prob->Xs) && aligned16(prob->Cs) &&
-                      aligned16(prob->idx_ii2jj) && aligned16(prob->Q) &&
-                      ((reinterpret_cast<uintptr_t>(prob->valid_match) & 3u) == 0);
+    a.P_ = make_params(prob);
     const size_t cap = static_cast<size_t>(kNumSMs) * 2;
     const int grid = static_cast<int>(items < cap ? items : cap);
-    if (prob->kind == M3R_GN_RAYS) launch_accumulate<M3R_GN_RAYS>(a, vec4, grid, s);
-    else if (prob->kind == M3R_GN_CALIB) launch_accumulate<M3R_GN_CALIB>(a, vec4, grid, s);
-    else launch_accumulate<M3R_GN_POINTS>(a, vec4, grid, s);
+    static bool attr_set = false;  // benign race: idempotent
+    if (!attr_set) {
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_kernel<M3R_GN_RAYS>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kAccSmemBytes));
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_kernel<M3R_GN_CALIB>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kAccSmemBytes));
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_kernel<M3R_GN_POINTS>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kAccSmemBytes));
+      attr_set = true;
+    }
+    if (prob->kind == M3R_GN_RAYS)
+      gn_accumulate_kernel<M3R_GN_RAYS><<<grid, kAccThreads, kAccSmemBytes, s>>>(a);
+    else if (prob->kind == M3R_GN_CALIB)
+      gn_accumulate_kernel<M3R_GN_CALIB><<<grid, kAccThreads, kAccSmemBytes, s>>>(a);
+    else
+      gn_accumulate_kernel<M3R_GN_POINTS><<<grid, kAccThreads, kAccSmemBytes, s>>>(a);
     M3R_LAUNCH_CHECK("gn_accumulate_kernel");
 
     gn_edge_finalize_kernel<<<ES, 64, 0, s>>>(ws->partials.p, prob->Twc, ws->pose_i.p,
