@@ -223,19 +223,20 @@ def gn_kwargs(g, D):
                 sigma_point=D["sigma_point"], C_thresh=D["C_thresh"], Q_thresh=D["Q_thresh"])
 
 
-def time_gn(g, D, kind, rank, world, iters=10, reps=3):
+def time_gn(g, D, kind, rank, world, iters=10, reps=3, exchange="peer"):
     """One gauss_newton_<kind> solve of `iters` iterations (delta_thresh = 0), through the
     staged C ABI so that the accumulation/assembly half and the solve half of every iteration
     get their own CUDA events.  At world > 1 each rank linearises its edge shard and the fp64
-    systems are all-reduced (NCCL) before the replicated solve."""
-    from mast3r_slam_backends.staged import StagedGN, shard_range
-    import torch.distributed as dist
+    systems are summed over the ranks before the replicated solve: `exchange` = "peer" (this
+    library's NVLink peer-memory kernels) or "nccl" (torch.distributed all_reduce)."""
+    from mast3r_slam_backends.staged import PeerExchange, StagedGN, TorchAllReduce, shard_range
 
     E = g["E"]
     b0, b1 = shard_range(E, rank, world)
     idx = g["idx_ii2jj"][b0:b1].contiguous()
     val = g["valid_match"][b0:b1].contiguous()
     Q = g["Q"][b0:b1].contiguous()
+    ex = PeerExchange(g["N"]) if (world > 1 and exchange == "peer") else TorchAllReduce()
     best = None
     for rep in range(reps + 1):  # first repetition is the warm-up
         Twc = g["Twc_init"].clone()
@@ -245,15 +246,15 @@ def time_gn(g, D, kind, rank, world, iters=10, reps=3):
         barrier(world)
         torch.cuda.synchronize()
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(iters)]
-        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0, t1, tb = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         t0.record()
         gn.begin()
+        tb.record()
         for i in range(iters):
             ev[i][0].record()
-            gn.linearize()
+            gn.linearize(into=ex.round_buffer(gn))
             ev[i][1].record()
-            if world > 1:
-                dist.all_reduce(gn.system, op=dist.ReduceOp.SUM)
+            ex.allreduce(gn)
             ev[i][2].record()
             gn.solve_retract(0.0)
             ev[i][3].record()
@@ -263,7 +264,7 @@ def time_gn(g, D, kind, rank, world, iters=10, reps=3):
         if rep == 0:
             continue
         total = max_over_ranks(t0.elapsed_time(t1), world)
-        r = dict(total_ms=total,
+        r = dict(total_ms=total, begin_ms=t0.elapsed_time(tb),
                  linearize_ms=statistics.mean(e[0].elapsed_time(e[1]) for e in ev),
                  allreduce_ms=statistics.mean(e[1].elapsed_time(e[2]) for e in ev),
                  solve_ms=statistics.mean(e[2].elapsed_time(e[3]) for e in ev),
@@ -418,7 +419,12 @@ def main():
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     torch.cuda.set_device(local_rank)
+    saved_stdout = None
     if world > 1:
+        # NCCL writes its version banner to stdout; stdout must carry the one JSON line only
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     M, D = synth.MATCH_DEFAULTS, synth.GN_DEFAULTS
     peak, peak_src = peaks()
@@ -462,7 +468,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": "px/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / e2e_steps},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "refine_f16_kernel<24>", "achieved": refine_gbs,
+        "roofline": {"bound": "hbm", "kernel": "refine_f16_tiled_kernel", "achieved": refine_gbs,
                      "peak": peak, "unit": "GB/s", "frac": refine_gbs / peak, "traffic": None,
                      "peak_source": peak_src,
                      "note": "algorithmic 128 B/point; the kernel is bound by half2 issue and L1 "
@@ -500,6 +506,12 @@ def main():
                          "traffic": None, "bytes_per_iter": gn_bytes,
                          "whole_iter_frac": gn_bytes / world / (gr["total_ms"] / 10 * 1e-3) / 1e9 / peak},
         }
+        line["gn"]["begin_ms"] = gr["begin_ms"]
+        line["gn"]["exchange"] = "none" if world == 1 else "NVLink peer memory (m3r_gn_comm_*), fp64 system"
+        if world > 1:  # the same sharded solve with torch.distributed's NCCL all-reduce, beside it
+            gn2 = time_gn(g, D, args.gn_kind, rank, world, reps=2, exchange="nccl")
+            line["gn"]["nccl_variant"] = {"ms_per_iter": gn2["total_ms"] / 10,
+                                          "allreduce_ms": gn2["allreduce_ms"]}
         if world == 1:
             ms_call, Tcall = time_gn_single_call(be, g, D, args.gn_kind)
             line["gn"]["single_call_ms_per_iter"] = ms_call / 10
@@ -515,9 +527,13 @@ def main():
             s_it, Ecpu = cpu_baseline_gn(D)
             line["cpu_baseline"]["gn_iters_per_s_64kf_extrapolated"] = 1.0 / (s_it * g["E"] / Ecpu)
             line["cpu_baseline"]["gn_sample"] = f"1 iteration, 8-keyframe graph ({Ecpu} edges), scaled by edges"
+    if saved_stdout is not None:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        os.dup2(2, 1)
         torch.distributed.destroy_process_group()
 
 

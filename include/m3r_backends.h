@@ -199,6 +199,45 @@ int m3r_gn_edge_blocks(m3r_gn_workspace *ws, const double **Hjj, const double **
  * synchronises `stream` (it reads a device counter); it is for tests and benchmarks. */
 int m3r_gn_iterations_done(m3r_gn_workspace *ws, void *stream, int *iters);
 
+/* ---------------------------------------------------------------------------------------
+ * Multi-GPU exchange of the assembled systems over NVLink peer memory (new; the reference
+ * is single-GPU).  One process per GPU.  Every rank owns an exchange area allocated by this
+ * library (two system buffers, used alternately, plus one arrival flag per peer) and maps
+ * the areas of all peers through CUDA IPC.  Per Gauss-Newton iteration a rank
+ *   1. linearises its edge shard straight into its own exchange buffer
+ *      (m3r_gn_linearize with system = m3r_gn_comm_system()),
+ *   2. m3r_gn_comm_signal: publishes "my buffer of this round is complete" into every
+ *      peer's flag array (system-scope release store after a system fence),
+ *   3. m3r_gn_comm_reduce: waits for all peers' flags of this round, then sums the W buffers
+ *      in rank order (bitwise identical result on every rank, so the replicated solves stay
+ *      in lockstep with no broadcast) into `out`, reading the peers' buffers directly over
+ *      NVLink,
+ *   4. m3r_gn_solve_retract on `out`.
+ * Two buffers suffice: a rank reaches round t+2 only after every peer has signalled round
+ * t+1, i.e. after it finished reading round t.
+ * Both kernels are no-ops once the workspace's stop flag is set (all ranks agree on it).
+ * ------------------------------------------------------------------------------------- */
+typedef struct m3r_gn_comm m3r_gn_comm;
+#define M3R_IPC_HANDLE_BYTES 64
+
+/* Allocates the exchange area for systems of up to `max_system_doubles` doubles. */
+int m3r_gn_comm_create(m3r_gn_comm **out, int rank, int world_size, int64_t max_system_doubles);
+void m3r_gn_comm_destroy(m3r_gn_comm *comm);
+/* IPC handle of this rank's exchange area (M3R_IPC_HANDLE_BYTES bytes), to be all-gathered. */
+int m3r_gn_comm_handle(m3r_gn_comm *comm, void *handle_out);
+/* `handles`: world_size consecutive handles in rank order (own entry ignored). */
+int m3r_gn_comm_connect(m3r_gn_comm *comm, const void *handles);
+/* Single-process variant for tests: connect communicators that live in the same process
+ * (one per device, peer access enabled by the call). */
+int m3r_gn_comm_connect_local(m3r_gn_comm **comms, int world_size);
+/* Starts the next exchange round and returns this rank's buffer for it. */
+int m3r_gn_comm_next_round(m3r_gn_comm *comm, double **system_out);
+int m3r_gn_comm_signal(m3r_gn_comm *comm, m3r_gn_workspace *ws, void *stream);
+/* out (m3r_gn_system_size(num_poses) doubles): block-lower triangle and right-hand side of
+ * the summed system, i.e. everything m3r_gn_solve_retract reads. */
+int m3r_gn_comm_reduce(m3r_gn_comm *comm, m3r_gn_workspace *ws, double *out, int num_poses,
+                       void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -297,7 +297,7 @@ struct Residual<M3R_GN_CALIB> {
 // stay bitwise reproducible.
 constexpr int kAccThreads = 256;
 constexpr int kAccWarps = kAccThreads / 32;
-constexpr int kSeg = 1024;                  // points per warp segment
+constexpr int kSeg = 2048;                  // points per warp segment
 constexpr int kChunk = kSeg * kAccWarps;    // points per work item (one CTA pass)
 
 __global__ void __launch_bounds__(256)
@@ -1064,6 +1064,8 @@ struct m3r_gn_workspace {
   int begun_shard_begin = -1, begun_shard_end = -1, begun_points = -1;
 };
 
+#include "gn_comm.cuh"
+
 extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
   M3R_REQUIRE(out != nullptr, "gn_workspace_create: null out pointer");
   m3r_gn_workspace *ws = new m3r_gn_workspace();
@@ -1231,7 +1233,8 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
     a.P_ = make_params(prob);
     const size_t cap = static_cast<size_t>(kNumSMs) * 2;
     const int grid = static_cast<int>(items < cap ? items : cap);
-    static bool attr_set = false;  // benign race: idempotent
+    static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
+    bool &attr_set = attr_set_dev[ws->device & 63];
     if (!attr_set) {
       M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_kernel<M3R_GN_RAYS>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kAccSmemBytes));
@@ -1349,6 +1352,10 @@ extern "C" int m3r_gn_iterations_done(m3r_gn_workspace *ws, void *stream, int *i
   M3R_CUDA_TRY(cudaMemcpyAsync(host, ws->flags, sizeof(host), cudaMemcpyDeviceToHost, s));
   M3R_CUDA_TRY(cudaStreamSynchronize(s));
   *iters = host[1];
+  if (host[3] != 0) {
+    set_error("gn: a multi-GPU exchange timed out waiting for a peer");
+    return M3R_ERR_CUDA;
+  }
   return M3R_OK;
 }
 

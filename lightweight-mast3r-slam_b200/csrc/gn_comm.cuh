@@ -1,0 +1,229 @@
+// Multi-GPU exchange of the assembled Gauss-Newton systems over NVLink peer memory
+// (include/m3r_backends.h, "Multi-GPU exchange").  Included by gn.cu after the workspace.
+//
+// One-shot all-reduce, written for this payload (0.8 MB of fp64 at 64 keyframes, 12.8 MB at
+// 256): every rank reads the W-1 remote buffers directly through NVLink and adds them in rank
+// order, so all ranks obtain bitwise identical sums and the replicated Cholesky solves stay in
+// lockstep.  One arrival flag per (reader, writer) pair carries the round number; buffers are
+// double-buffered by round parity, which makes a second barrier unnecessary (header comment).
+#pragma once
+
+namespace m3r {
+
+constexpr int kCommMaxWorld = 16;
+constexpr int kCommFlagBytes = 1024;  // flag block at the start of the exchange area
+
+__device__ __forceinline__ int ld_acquire_sys(const int *p) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(int *p, int v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ double2 ld_relaxed_sys_f64x2(const double *p) {
+  double2 v;
+  asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys_f64(const double *p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+
+struct CommTable {
+  int *flags[kCommMaxWorld];            // flags[p]: flag block of rank p (peer-mapped)
+  const double *buf[2][kCommMaxWorld];  // buf[parity][p]: system buffer of rank p
+};
+
+// "my buffer of round `round` is complete": one release store per peer.  The buffer was written
+// by earlier kernels on this stream (visible at the device's L2, which is where peer reads land).
+__global__ void comm_signal_kernel(const CommTable T, int rank, int world, int round,
+                                   const int *__restrict__ stop) {
+  if (stop[0]) return;
+  const int p = threadIdx.x;
+  if (p < world) {
+    __threadfence_system();
+    st_release_sys(T.flags[p] + rank, round);
+  }
+}
+
+// Wait for every rank's flag of this round, then out = sum over ranks (rank order) of the
+// systems: the block-lower triangle of the D x D matrix (the only part the solver reads; a
+// block row is 7 scalar rows) and the D right-hand-side entries behind it.  One CTA per
+// scalar row, remote rows read as coalesced 8-byte loads over NVLink.
+__global__ void __launch_bounds__(256)
+    comm_reduce_kernel(const CommTable T, int rank, int world, int round, double *__restrict__ out,
+                       int D, int *__restrict__ ws_flags) {
+  if (ws_flags[0]) return;
+  __shared__ int timed_out;
+  if (threadIdx.x == 0) timed_out = 0;
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const int *f = T.flags[rank] + threadIdx.x;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(f) < round) {
+      if (clock64() - t0 > 8000000000LL) {  // ~4 s: a peer died; do not hang the GPU
+        timed_out = 1;
+        break;
+      }
+      __nanosleep(100);
+    }
+  }
+  __syncthreads();
+  if (timed_out) {
+    if (threadIdx.x == 0) ws_flags[3] = 1;
+    return;
+  }
+  const int par = round & 1;
+  for (int r = blockIdx.x; r <= D; r += gridDim.x) {  // row D = the right-hand side
+    const int len = (r < D) ? 7 * (r / 7 + 1) : D;
+    const size_t off = static_cast<size_t>(r) * D;
+    for (int c = threadIdx.x; c < len; c += blockDim.x) {
+      double s = 0.0;
+      for (int p = 0; p < world; p++) s += ld_relaxed_sys_f64(T.buf[par][p] + off + c);
+      out[off + c] = s;
+    }
+  }
+}
+
+}  // namespace m3r
+
+struct m3r_gn_comm {
+  int device = 0, rank = 0, world = 1;
+  long long cap = 0;          // doubles per system buffer (even)
+  unsigned char *area = nullptr;  // [flags | buf0 | buf1], cudaMalloc'ed here
+  void *peer_area[m3r::kCommMaxWorld] = {nullptr};
+  bool opened[m3r::kCommMaxWorld] = {false};  // mapped through cudaIpcOpenMemHandle
+  bool connected = false;
+  int round = 0;
+  m3r::CommTable table{};
+};
+
+static size_t comm_area_bytes(long long cap) {
+  return static_cast<size_t>(m3r::kCommFlagBytes) + 2 * static_cast<size_t>(cap) * sizeof(double);
+}
+
+static void comm_fill_table(m3r_gn_comm *c) {
+  for (int p = 0; p < c->world; p++) {
+    unsigned char *base = static_cast<unsigned char *>(c->peer_area[p]);
+    c->table.flags[p] = reinterpret_cast<int *>(base);
+    c->table.buf[0][p] = reinterpret_cast<const double *>(base + m3r::kCommFlagBytes);
+    c->table.buf[1][p] = c->table.buf[0][p] + c->cap;
+  }
+  c->connected = true;
+}
+
+extern "C" int m3r_gn_comm_create(m3r_gn_comm **out, int rank, int world_size,
+                                  int64_t max_system_doubles) {
+  M3R_REQUIRE(out != nullptr, "gn_comm_create: null out pointer");
+  M3R_REQUIRE(world_size >= 1 && world_size <= m3r::kCommMaxWorld && rank >= 0 && rank < world_size,
+              "gn_comm_create: bad rank %d / world size %d (max %d)", rank, world_size,
+              m3r::kCommMaxWorld);
+  M3R_REQUIRE(max_system_doubles > 0, "gn_comm_create: empty system");
+  m3r_gn_comm *c = new m3r_gn_comm();
+  c->rank = rank, c->world = world_size;
+  c->cap = (max_system_doubles + 1) & ~1LL;
+  cudaError_t e = cudaGetDevice(&c->device);
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&c->area), comm_area_bytes(c->cap));
+  if (e == cudaSuccess) e = cudaMemset(c->area, 0, comm_area_bytes(c->cap));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    delete c;
+    return m3r::cuda_fail(e, "gn_comm_create");
+  }
+  c->peer_area[rank] = c->area;
+  if (world_size == 1) comm_fill_table(c);
+  *out = c;
+  return M3R_OK;
+}
+
+extern "C" void m3r_gn_comm_destroy(m3r_gn_comm *c) {
+  if (!c) return;
+  for (int p = 0; p < c->world; p++)
+    if (c->opened[p]) cudaIpcCloseMemHandle(c->peer_area[p]);
+  cudaFree(c->area);
+  delete c;
+}
+
+extern "C" int m3r_gn_comm_handle(m3r_gn_comm *c, void *handle_out) {
+  M3R_REQUIRE(c && handle_out, "gn_comm_handle: null pointer");
+  static_assert(sizeof(cudaIpcMemHandle_t) == M3R_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  M3R_CUDA_TRY(cudaIpcGetMemHandle(&h, c->area));
+  memcpy(handle_out, &h, sizeof(h));
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_comm_connect(m3r_gn_comm *c, const void *handles) {
+  M3R_REQUIRE(c && handles, "gn_comm_connect: null pointer");
+  for (int p = 0; p < c->world; p++) {
+    if (p == c->rank || c->opened[p]) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const unsigned char *>(handles) + static_cast<size_t>(p) * sizeof(h), sizeof(h));
+    void *ptr = nullptr;
+    M3R_CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_area[p] = ptr;
+    c->opened[p] = true;
+  }
+  comm_fill_table(c);
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_comm_connect_local(m3r_gn_comm **comms, int world_size) {
+  M3R_REQUIRE(comms && world_size >= 1 && world_size <= m3r::kCommMaxWorld, "gn_comm_connect_local: bad arguments");
+  int cur = 0;
+  M3R_CUDA_TRY(cudaGetDevice(&cur));
+  for (int a = 0; a < world_size; a++) {
+    M3R_REQUIRE(comms[a] && comms[a]->world == world_size && comms[a]->rank == a,
+                "gn_comm_connect_local: communicator %d does not match", a);
+    M3R_CUDA_TRY(cudaSetDevice(comms[a]->device));
+    for (int b = 0; b < world_size; b++) {
+      if (comms[b]->device == comms[a]->device) continue;
+      cudaError_t e = cudaDeviceEnablePeerAccess(comms[b]->device, 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+      else if (e != cudaSuccess) {
+        cudaSetDevice(cur);
+        return m3r::cuda_fail(e, "cudaDeviceEnablePeerAccess");
+      }
+    }
+  }
+  M3R_CUDA_TRY(cudaSetDevice(cur));
+  for (int a = 0; a < world_size; a++) {
+    for (int b = 0; b < world_size; b++) comms[a]->peer_area[b] = comms[b]->area;
+    comm_fill_table(comms[a]);
+  }
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_comm_next_round(m3r_gn_comm *c, double **system_out) {
+  M3R_REQUIRE(c && system_out, "gn_comm_next_round: null pointer");
+  M3R_REQUIRE(c->connected, "gn_comm_next_round: communicator is not connected");
+  c->round += 1;
+  *system_out = const_cast<double *>(c->table.buf[c->round & 1][c->rank]);
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_comm_signal(m3r_gn_comm *c, m3r_gn_workspace *ws, void *stream) {
+  M3R_REQUIRE(c && ws, "gn_comm_signal: null pointer");
+  M3R_REQUIRE(c->connected && c->round > 0, "gn_comm_signal: no round in progress");
+  m3r::comm_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->table, c->rank, c->world,
+                                                                         c->round, ws->flags);
+  M3R_LAUNCH_CHECK("comm_signal_kernel");
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *out, int num_poses,
+                                  void *stream) {
+  M3R_REQUIRE(c && ws && out, "gn_comm_reduce: null pointer");
+  M3R_REQUIRE(c->connected && c->round > 0, "gn_comm_reduce: no round in progress");
+  M3R_REQUIRE(num_poses >= 2 && m3r_gn_system_size(num_poses) <= c->cap,
+              "gn_comm_reduce: system of %d poses exceeds the exchange area", num_poses);
+  const int D = 7 * (num_poses - 1);
+  const int blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
+  m3r::comm_reduce_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      c->table, c->rank, c->world, c->round, out, D, ws->flags);
+  M3R_LAUNCH_CHECK("comm_reduce_kernel");
+  return M3R_OK;
+}

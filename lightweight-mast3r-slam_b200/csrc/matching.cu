@@ -678,7 +678,10 @@ extern "C" int m3r_refine_matches_v(const void *D11, const void *D21, const int6
     const bool tiled = fast && variant == 0 && radius == 3 && dilation_max >= 1 &&
                        static_cast<long long>(n) == static_cast<long long>(h) * w;
     if (tiled) {
-      static bool attr_set = false;  // benign race: idempotent
+      static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
+      int dev = 0;
+      M3R_CUDA_TRY(cudaGetDevice(&dev));
+      bool &attr_set = attr_set_dev[dev & 63];
       if (!attr_set) {
         M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));

@@ -123,6 +123,16 @@ gn_iterations_done = _sig(
     "m3r_gn_iterations_done", c_int, [c_void_p, c_void_p, ctypes.POINTER(c_int)]
 )
 
+IPC_HANDLE_BYTES = 64
+gn_comm_create = _sig("m3r_gn_comm_create", c_int, [ctypes.POINTER(c_void_p), c_int, c_int, c_int64])
+gn_comm_destroy = _sig("m3r_gn_comm_destroy", None, [c_void_p])
+gn_comm_handle = _sig("m3r_gn_comm_handle", c_int, [c_void_p, c_void_p])
+gn_comm_connect = _sig("m3r_gn_comm_connect", c_int, [c_void_p, c_void_p])
+gn_comm_connect_local = _sig("m3r_gn_comm_connect_local", c_int, [ctypes.POINTER(c_void_p), c_int])
+gn_comm_next_round = _sig("m3r_gn_comm_next_round", c_int, [c_void_p, ctypes.POINTER(c_void_p)])
+gn_comm_signal = _sig("m3r_gn_comm_signal", c_int, [c_void_p, c_void_p, c_void_p])
+gn_comm_reduce = _sig("m3r_gn_comm_reduce", c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p])
+
 # every symbol include/m3r_backends.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "m3r_abi_version",
@@ -143,6 +153,14 @@ EXPORTS = [
     "m3r_gn_solve_retract",
     "m3r_gn_edge_blocks",
     "m3r_gn_iterations_done",
+    "m3r_gn_comm_create",
+    "m3r_gn_comm_destroy",
+    "m3r_gn_comm_handle",
+    "m3r_gn_comm_connect",
+    "m3r_gn_comm_connect_local",
+    "m3r_gn_comm_next_round",
+    "m3r_gn_comm_signal",
+    "m3r_gn_comm_reduce",
 ]
 
 

@@ -74,10 +74,13 @@ class StagedGN:
         with torch.cuda.device(self.dev):
             _lib.check(_lib.gn_begin(self.ws.handle, ctypes.byref(self.prob), _stream()), "gn_begin")
 
-    def linearize(self):
+    def linearize(self, into=None):
+        """Accumulate this shard and assemble the dense system into `self.system`, or into the
+        device buffer at address `into` (an exchange buffer of PeerExchange)."""
+        dst = _ptr(self.system) if into is None else ctypes.c_void_p(int(into))
         with torch.cuda.device(self.dev):
-            _lib.check(_lib.gn_linearize(self.ws.handle, ctypes.byref(self.prob),
-                                         _ptr(self.system), _stream()), "gn_linearize")
+            _lib.check(_lib.gn_linearize(self.ws.handle, ctypes.byref(self.prob), dst, _stream()),
+                       "gn_linearize")
 
     def solve_retract(self, delta_thresh=0.0):
         with torch.cuda.device(self.dev):
@@ -123,12 +126,90 @@ def _from_ptr(ptr, shape, device):
         return torch.as_tensor(_CudaArray(ptr, shape, "<f8"), device=device)
 
 
+class TorchAllReduce:
+    """Exchange through torch.distributed (NCCL on GPUs, gloo in the CPU tests): one
+    all_reduce(sum) of the assembled system per iteration."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def round_buffer(self, stage):
+        return None  # linearise into stage.system
+
+    def allreduce(self, stage):
+        import torch.distributed as dist
+
+        if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(stage.system, op=dist.ReduceOp.SUM, group=self.group)
+
+
+class PeerExchange:
+    """Exchange through this library's own NVLink peer-memory kernels (m3r_gn_comm_*,
+    include/m3r_backends.h): each rank linearises straight into its exchange buffer, flags it
+    complete in every peer, and sums all ranks' buffers in rank order into its local system.
+    One process per GPU; the exchange areas are mapped across processes with CUDA IPC, the
+    handles travel once through torch.distributed at construction."""
+
+    def __init__(self, num_poses, group=None, device=None):
+        import torch.distributed as dist
+
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        self.size = int(_lib.gn_system_size(num_poses))
+        self.handle = ctypes.c_void_p()
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.gn_comm_create(ctypes.byref(self.handle), self.rank, self.world, self.size),
+                       "gn_comm_create")
+            if self.world > 1:
+                mine = (ctypes.c_ubyte * _lib.IPC_HANDLE_BYTES)()
+                _lib.check(_lib.gn_comm_handle(self.handle, mine), "gn_comm_handle")
+                gathered = [None] * self.world
+                dist.all_gather_object(gathered, bytes(mine), group=group)
+                blob = b"".join(gathered)
+                buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+                _lib.check(_lib.gn_comm_connect(self.handle, buf), "gn_comm_connect")
+                dist.barrier(group=group)  # nobody signals into an area that is not mapped yet
+
+    def __del__(self):
+        try:
+            if self.handle:
+                _lib.gn_comm_destroy(self.handle)
+        except Exception:
+            pass
+
+    def round_buffer(self, stage):
+        ptr = ctypes.c_void_p()
+        _lib.check(_lib.gn_comm_next_round(self.handle, ctypes.byref(ptr)), "gn_comm_next_round")
+        return ptr.value
+
+    def allreduce(self, stage):
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.gn_comm_signal(self.handle, stage.ws.handle, _stream()), "gn_comm_signal")
+            _lib.check(_lib.gn_comm_reduce(self.handle, stage.ws.handle, _ptr(stage.system),
+                                           stage.N, _stream()), "gn_comm_reduce")
+
+
+def run_spmd(stage, exchange, max_iter, delta_thresh):
+    """The SPMD Gauss-Newton loop every rank runs: linearise the own shard, sum the systems over
+    the ranks, solve and retract the replica.  `stage` offers begin / linearize(into) /
+    solve_retract / system (StagedGN here; the CPU tests plug in an oracle-backed stage)."""
+    stage.begin()
+    for _ in range(int(max_iter)):
+        stage.linearize(into=exchange.round_buffer(stage))
+        exchange.allreduce(stage)
+        stage.solve_retract(delta_thresh)
+
+
 def gauss_newton_sharded(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_shard, *,
-                         max_iter, delta_thresh, group=None, **params):
+                         max_iter, delta_thresh, group=None, exchange=None, **params):
     """SPMD Gauss-Newton: call on every rank of `group` with the same replicated tensors and
     this rank's shard of the edge data (rows `shard_range(E, rank, world)`).
 
-    Returns [dx]; Twc is updated in place on every rank (bitwise identical replicas)."""
+    `exchange`: a PeerExchange (NVLink peer memory, default when world > 1 is not given: NCCL)
+    or TorchAllReduce.  Returns ([dx], stage); Twc is updated in place on every rank (bitwise
+    identical replicas)."""
     import torch.distributed as dist
 
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -136,10 +217,5 @@ def gauss_newton_sharded(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_sh
     begin, end = shard_range(ii.shape[0], rank, world)
     gn = StagedGN(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_shard,
                   edge_begin=begin, edge_end=end, **params)
-    gn.begin()
-    for _ in range(int(max_iter)):
-        gn.linearize()
-        if world > 1:
-            dist.all_reduce(gn.system, op=dist.ReduceOp.SUM, group=group)
-        gn.solve_retract(delta_thresh)
+    run_spmd(gn, exchange if exchange is not None else TorchAllReduce(group), max_iter, delta_thresh)
     return [gn.dx], gn
