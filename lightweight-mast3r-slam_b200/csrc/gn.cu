@@ -970,6 +970,7 @@ __global__ void __launch_bounds__(kSolveThreads)
 }
 
 #include "gn_chol_coop.cuh"
+#include "gn_chol_cluster.cuh"
 
 // ----------------------------------------------------------------------------------------
 // keyframe id -> packed pose index (sorted-unique rank), no host sync
@@ -1274,10 +1275,31 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
   const int D = 7 * (prob->num_poses - 1);
   if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
   if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride))) return rc;
-  static const bool use_multi = [] {
+  // M3R_GN_SOLVER = coop (default) | cluster (D <= 448 only; measured slower: 430 vs 340 us at
+  // D = 441, profiles/r1_d_cluster_solver_phases.txt) | multi   (benchmarks, tests)
+  static const int solver_choice = [] {
     const char *e = getenv("M3R_GN_SOLVER");
-    return e && strcmp(e, "multi") == 0;
+    if (e && strcmp(e, "multi") == 0) return 2;
+    if (e && strcmp(e, "cluster") == 0) return 0;
+    return 1;
   }();
+  const bool use_multi = solver_choice == 2;
+  if (solver_choice == 0 && D <= kClMaxD) {
+    // one 8-CTA cluster, matrix resident in distributed shared memory
+    if ((rc = ws->xbuf.reserve(static_cast<size_t>(kClMaxD)))) return rc;
+    if ((rc = ws->ldiag.reserve(static_cast<size_t>(kClMaxD)))) return rc;
+    static bool attr_set_dev[64] = {false};
+    bool &attr_set = attr_set_dev[ws->device & 63];
+    if (!attr_set) {
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_chol_solve_cluster_kernel,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kClSmemBytes));
+      attr_set = true;
+    }
+    gn_chol_solve_cluster_kernel<<<kClSize, kClThreads, kClSmemBytes, s>>>(
+        system, ws->ldiag.p, D, ws->xbuf.p, prob->Twc, dx, prob->num_poses, delta_thresh, ws->flags);
+    M3R_LAUNCH_CHECK("gn_chol_solve_cluster_kernel");
+    return M3R_OK;
+  }
   if (!use_multi) {
     // one cooperative launch: Cholesky + substitutions + retraction + stop test
     static int max_coresident = 0;
@@ -1335,6 +1357,14 @@ extern "C" int m3r_debug_coop_profile(long long *out8) {
   M3R_CUDA_TRY(cudaDeviceSynchronize());
   M3R_CUDA_TRY(cudaMemcpyFromSymbol(out8, g_coop_prof, sizeof(zero)));
   M3R_CUDA_TRY(cudaMemcpyToSymbol(g_coop_prof, zero, sizeof(zero)));
+  return M3R_OK;
+}
+
+extern "C" int m3r_debug_cluster_profile(long long *out9) {
+  long long zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  M3R_CUDA_TRY(cudaDeviceSynchronize());
+  M3R_CUDA_TRY(cudaMemcpyFromSymbol(out9, g_cl_prof, sizeof(zero)));
+  M3R_CUDA_TRY(cudaMemcpyToSymbol(g_cl_prof, zero, sizeof(zero)));
   return M3R_OK;
 }
 

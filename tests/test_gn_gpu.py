@@ -102,6 +102,22 @@ def test_first_step_and_final_poses_vs_oracle(backends, oracle, kind, N, h, w, s
     assert e_dx < TOL and e_T1 < TOL and e_T10 < TOL
 
 
+@pytest.mark.parametrize("N", [64, 65, 70])
+def test_solver_paths_by_size(backends, oracle, N):
+    """D = 7(N-1) = 441 and 448 run on the 8-CTA cluster solver (matrix in distributed shared
+    memory), 483 on the grid-wide cooperative solver: same answers as the oracle's Eigen-style
+    fp64 solve."""
+    g = synth.make_graph(N, 24, 32, seed=6)
+    P = gn_params(oracle, "rays", g)
+    Twc = g["Twc_init"].cuda().clone()
+    (dx,) = _call(backends, "rays", g, Twc, 2, 0.0)
+    To, dxo, _ = oracle.gauss_newton(P, g["Twc_init"], g["Xs"], g["Cs"], g["ii"], g["jj"],
+                                     g["idx_ii2jj"], g["valid_match"], g["Q"], 2, 0.0)
+    e_dx, e_T = _rel(dx.cpu(), dxo), _pose_err(Twc.cpu(), To)
+    print(f"N={N} D={7 * (N - 1)}: rel err dx {e_dx:.2e}, Twc {e_T:.2e}")
+    assert e_dx < TOL and e_T < TOL
+
+
 def test_failed_factorisation_gives_zero_step(backends):
     """All matches invalid -> H = 0 -> Cholesky fails -> dx = 0 and Twc untouched
     (gn_kernels.cu:147-150), never NaN."""

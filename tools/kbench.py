@@ -39,7 +39,7 @@ def main():
         pass
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) == 1:
     main()
 
 
@@ -62,3 +62,24 @@ def coop_profile():
 
 if __name__ == "__main__" and "coop" in sys.argv:
     coop_profile()
+
+
+def cluster_profile():
+    """Per-phase cycles of the cluster Cholesky/solve kernel (CTA 0)."""
+    import ctypes
+    from mast3r_slam_backends import _lib
+    D = synth.GN_DEFAULTS
+    g = bench.make_gn_graph(int(os.environ.get("KF", 64)), "cuda")
+    out = (ctypes.c_longlong * 9)()
+    _lib.lib.m3r_debug_cluster_profile(out)
+    r = bench.time_gn(g, D, "rays", 0, 1, reps=1)
+    _lib.lib.m3r_debug_cluster_profile(out)
+    n = max(out[8], 1)
+    names = ["load", "potrf+wait", "trsm", "barrier2", "syrk", "barrier3", "backward", "finish"]
+    print(f"cluster solver: {out[8]} launches, solve_ms {r['solve_ms']:.3f}, linearize_ms {r['linearize_ms']:.3f}")
+    for k, nm in enumerate(names):
+        print(f"  {nm:11s} {out[k] / n / 1.965e3:8.1f} us per launch")
+
+
+if __name__ == "__main__" and "cluster" in sys.argv:
+    cluster_profile()
