@@ -103,10 +103,14 @@ def test_first_step_and_final_poses_vs_oracle(backends, oracle, kind, N, h, w, s
 
 
 @pytest.mark.parametrize("N", [64, 65, 70])
-def test_solver_paths_by_size(backends, oracle, N):
-    """D = 7(N-1) = 441 and 448 run on the 8-CTA cluster solver (matrix in distributed shared
-    memory), 483 on the grid-wide cooperative solver: same answers as the oracle's Eigen-style
-    fp64 solve."""
+def test_solver_by_system_size(backends, oracle, N):
+    """D = 7(N-1) = 441, 448, 483 (14, 14 and 16 panels of the blocked Cholesky): same answers
+    as the oracle's Eigen-style fp64 solve."""
+    e_dx, e_T = _solver_check(backends, oracle, N)
+    assert e_dx < TOL and e_T < TOL
+
+
+def _solver_check(backends, oracle, N):
     g = synth.make_graph(N, 24, 32, seed=6)
     P = gn_params(oracle, "rays", g)
     Twc = g["Twc_init"].cuda().clone()
@@ -115,7 +119,26 @@ def test_solver_paths_by_size(backends, oracle, N):
                                      g["idx_ii2jj"], g["valid_match"], g["Q"], 2, 0.0)
     e_dx, e_T = _rel(dx.cpu(), dxo), _pose_err(Twc.cpu(), To)
     print(f"N={N} D={7 * (N - 1)}: rel err dx {e_dx:.2e}, Twc {e_T:.2e}")
-    assert e_dx < TOL and e_T < TOL
+    return e_dx, e_T
+
+
+@pytest.mark.parametrize("solver", ["cluster", "multi"])
+def test_alternative_solvers(solver):
+    """The opt-in solvers (M3R_GN_SOLVER is read once per process): the 8-CTA cluster Cholesky
+    with the matrix in distributed shared memory, and the multi-launch blocked Cholesky."""
+    import subprocess
+    import sys
+
+    code = ("import sys; sys.path[:0] = %r\n"
+            "import torch, m3r_oracle, mast3r_slam_backends as be, test_gn_gpu as t\n"
+            "m3r_oracle.build()\n"
+            "for N in (5, 64):\n"
+            "    e_dx, e_T = t._solver_check(be, m3r_oracle, N)\n"
+            "    assert e_dx < t.TOL and e_T < t.TOL, (N, e_dx, e_T)\n"
+            "print('ok')\n") % [p for p in sys.path if p]
+    env = dict(os.environ, M3R_GN_SOLVER=solver)
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def test_failed_factorisation_gives_zero_step(backends):
