@@ -40,6 +40,14 @@ NUM_SETS = 8  # input sets rotated through the timed region: 8 x 38 MB > 126 MB 
 B_ITER_PROJ, B_REFINE, B_GN = 65, 128, 45
 
 
+def traffic(kernel):
+    """Measured DRAM bytes per launch of `kernel` (ncu --set full, profiles/traffic.json)."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[kernel]["bytes"])
+    except Exception:
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -469,12 +477,16 @@ def main():
                 "ms_per_step": e2e_ms / e2e_steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "refine_f16_tiled_kernel", "achieved": refine_gbs,
-                     "peak": peak, "unit": "GB/s", "frac": refine_gbs / peak, "traffic": None,
-                     "peak_source": peak_src,
-                     "note": "algorithmic 128 B/point; the kernel is bound by half2 issue and L1 "
-                             "wavefronts (245 windows x 24 individually rounded MACs per point), "
-                             "not by HBM",
-                     "half_mac_per_s": half_macs / (r["refine_ms"] * 1e-3)},
+                     "peak": peak, "unit": "GB/s", "frac": refine_gbs / peak,
+                     "traffic": traffic("refine_f16_tiled_kernel"), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": B_REFINE * N_PTS,
+                     "note": "bit-exactness fixes 245 windows x 24 individually rounded half MACs per "
+                             "point: the kernel is bound by the fp16x2 pipe (0.49 warp-instr/clk/SMSP "
+                             "measured, profiles/r1_ubench_pipes.txt) and shared-memory bandwidth, "
+                             "both 62 us per frame at 1965 MHz, not by HBM",
+                     "half_op_per_s": 2 * half_macs / (r["refine_ms"] * 1e-3),
+                     "fp16_pipe_frac": (2 * half_macs / 2 / 32) / (148 * 4 * 0.486 * 1.965e9) /
+                                       (r["refine_ms"] * 1e-3)},
         "kernels": {"iter_proj_ms": r["iter_proj_ms"], "cast_ms": r["cast_ms"], "refine_ms": r["refine_ms"],
                     "iter_proj_gbs": iproj_gbs, "iter_proj_frac": iproj_gbs / peak,
                     "pair_gbs": pair_gbs, "pair_frac": pair_gbs / peak},
@@ -501,9 +513,11 @@ def main():
             "ms_per_iter": gr["total_ms"] / 10, "linearize_ms": gr["linearize_ms"],
             "allreduce_ms": gr["allreduce_ms"], "solve_ms": gr["solve_ms"],
             "iters_done": gr["iters_done"], "gpu_launches": int(gn_launches),
-            "roofline": {"bound": "hbm", "kernel": "gn_accumulate_kernel (+finalize+assemble)",
+            "roofline": {"bound": "hbm", "kernel": "gn_accumulate_kernel (+edge finalize + assemble)",
                          "achieved": lin_gbs, "peak": peak, "unit": "GB/s", "frac": lin_gbs / peak,
-                         "traffic": None, "bytes_per_iter": gn_bytes,
+                         "traffic": traffic("gn_accumulate_kernel"), "bytes_per_iter": gn_bytes,
+                         "note": "algorithmic = 45 B x E x n (SURVEY 8d); the kernel reads compacted "
+                                 "lists and hits L2 on the pointmaps, so DRAM traffic is below it",
                          "whole_iter_frac": gn_bytes / world / (gr["total_ms"] / 10 * 1e-3) / 1e9 / peak},
         }
         line["gn"]["begin_ms"] = gr["begin_ms"]
