@@ -1302,13 +1302,19 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
   }
   if (!use_multi) {
     // one cooperative launch: Cholesky + substitutions + retraction + stop test
+    static bool coop_attr_dev[64] = {false};
+    if (!coop_attr_dev[ws->device & 63]) {
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_chol_solve_coop_kernel,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kCoopSmemBytes));
+      coop_attr_dev[ws->device & 63] = true;
+    }
     static int max_coresident = 0;
     if (max_coresident == 0) {
       int dev = 0, sms = 0, per_sm = 0;
       M3R_CUDA_TRY(cudaGetDevice(&dev));
       M3R_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
       M3R_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_chol_solve_coop_kernel,
-                                                                kCoopThreads, 0));
+                                                                kCoopThreads, kCoopSmemBytes));
       max_coresident = sms * (per_sm > 0 ? 1 : 0);  // one CTA per SM keeps the barrier cheap
       if (max_coresident <= 0) {
         set_error("gn_solve_retract: cooperative kernel cannot be resident");
@@ -1317,9 +1323,8 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     }
     const int m0 = D - kPB > 0 ? D - kPB : 0;
     const int T0 = (m0 + 31) / 32;  // 32x32 tiles of the first trailing update
-    int want = T0 * (T0 + 1) / 2;
     const int row_ctas = (m0 + kTrsmRows - 1) / kTrsmRows;
-    if (want < row_ctas) want = row_ctas;
+    int want = T0 * (T0 + 1) / 2 + row_ctas;  // update CTAs + panel CTAs (look-ahead)
     if (want < 1) want = 1;
     const int grid = want < max_coresident ? want : max_coresident;
     double *sys_p = system, *ld_p = ws->ldiag.p, *x_p = ws->xbuf.p;
@@ -1329,7 +1334,7 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     int *fl = ws->flags;
     void *args[] = {&sys_p, &ld_p, &D_, &x_p, &twc_p, &dx_p, &np, &dth, &fl};
     M3R_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(gn_chol_solve_coop_kernel),
-                                             dim3(grid), dim3(kCoopThreads), args, 0, s));
+                                             dim3(grid), dim3(kCoopThreads), args, kCoopSmemBytes, s));
     g_launch_count.fetch_add(1, std::memory_order_relaxed);
     return M3R_OK;
   }
@@ -1352,8 +1357,8 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
 }
 
 // debug: cumulative per-phase cycle counts of the cooperative solver (CTA 0), then reset
-extern "C" int m3r_debug_coop_profile(long long *out8) {
-  long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+extern "C" int m3r_debug_coop_profile(long long *out8) {  // 16 entries
+  long long zero[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   M3R_CUDA_TRY(cudaDeviceSynchronize());
   M3R_CUDA_TRY(cudaMemcpyFromSymbol(out8, g_coop_prof, sizeof(zero)));
   M3R_CUDA_TRY(cudaMemcpyToSymbol(g_coop_prof, zero, sizeof(zero)));

@@ -100,7 +100,7 @@ __global__ void __cluster_dims__(kClSize, 1, 1) __launch_bounds__(kClThreads, 1)
       double a[kPB];
 #pragma unroll
       for (int cc = 0; cc < kPB; cc++) a[cc] = (cc <= lane) ? blkk[lane * ld + k * kPB + cc] : 0.0;
-      warp_chol32(a, lane, S.dinv, &S.bad);
+      warp_chol32(a, lane, S.stage[0][0], S.dinv, &S.bad);
 #pragma unroll
       for (int cc = 0; cc < kPB; cc++) {
         S.L11[lane][cc] = (cc <= lane) ? a[cc] : 0.0;

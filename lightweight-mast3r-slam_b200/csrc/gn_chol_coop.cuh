@@ -4,13 +4,14 @@
 // stop test.  Replaces 2*ceil(D/32)+1 dependent launches by one launch with two grid-wide
 // barriers per 32-column panel.  (Included by gn.cu inside namespace m3r.)
 //
-// Per panel k (columns k0..k0+pb):
-//   phase A  every CTA that owns rows of the panel factors the pb x pb diagonal block
-//            redundantly (one warp, rows in registers, shuffles; no barrier between POTRF and
-//            TRSM), solves y_k = L11^-1 b_k, then its rows: L21 = A21 L11^-T, b_r -= L21 y_k.
-//            CTA 0 stores L11 to `ldiag` (not in place: other CTAs are still reading A11).
-//   grid.sync
-//   phase B  A22 -= L21 L21^T on the lower tiles (32x32 or 64x64), strided over the CTAs.
+// Per panel k (columns k0..k0+pb), ONE grid barrier per panel (look-ahead):
+//   phase A  (panel CTAs: one per 128 rows below the panel)  folds the previous panel's
+//            trailing update into this panel's columns while loading them, factors the
+//            pb x pb diagonal block redundantly (one warp, rows in registers, shuffles; no
+//            barrier between POTRF and TRSM), solves y_k = L11^-1 b_k, then its rows:
+//            L21 = A21 L11^-T, b_r -= L21 y_k.  CTA 0 stores L11 to `ldiag`.
+//   phase B  (all other CTAs, at the same time)  A22 -= L21 L21^T of the PREVIOUS panel on the
+//            rows/columns behind this panel, lower tiles 32x32 or 64x64.
 //   grid.sync
 // After the last panel CTA 0 runs the backward substitution L^T x = y (column oriented: every
 // step is one round of independent, coalesced loads) and finish_step().
@@ -20,13 +21,24 @@ namespace cg = ::cooperative_groups;  // <cooperative_groups.h> is included by g
 
 // cycles CTA 0 spent in: [0] phase A, [1] barrier 1, [2] phase B, [3] barrier 2, [4] backward
 // substitution, [5] finish_step; [6] launches.  Read by m3r_debug_coop_profile (tools/).
-__device__ long long g_coop_prof[8];
+__device__ long long g_coop_prof[16];  // [8..13]: phase A split of CTA 0, see COOP_ATICK
 #define COOP_TICK(slot)                                   \
   do {                                                    \
     if (blockIdx.x == 0 && threadIdx.x == 0) {            \
       const long long now_ = clock64();                   \
       prof_acc[slot] += now_ - prof_t;                    \
       prof_t = now_;                                      \
+    }                                                     \
+  } while (0)
+
+// phase A of CTA 0, thread 0 (warp 0): [8] stage previous L21, [9] loads + look-ahead update,
+// [10] POTRF, [11] y_k chain + stores, [12] waiting for the TRSM warps, [13] rhs update
+#define COOP_ATICK(slot)                                  \
+  do {                                                    \
+    if (blockIdx.x == 0 && threadIdx.x == 0) {            \
+      const long long now_ = clock64();                   \
+      aprof[slot - 8] += now_ - aprof_t;                  \
+      aprof_t = now_;                                     \
     }                                                     \
   } while (0)
 
@@ -37,7 +49,6 @@ constexpr int kTrsmRows = 128;  // panel rows per CTA in phase A (warps 1..4, on
 // 1/sqrt(d) to fp64 accuracy from the fp32 MUFU.RSQ seed and two Newton steps: this sits on
 // the pivot chain of the factorisation (D sequential pivots), so its latency matters.
 __device__ __forceinline__ double chain_rsqrt(double d) {
-  if (d < 1e-30 || d > 1e30) return rsqrt(d);
   double r = static_cast<double>(rsqrtf(__double2float_rn(d)));
   double e = fma(-d * r, r, 1.0);
   r = fma(0.5 * r, e, r);
@@ -46,28 +57,38 @@ __device__ __forceinline__ double chain_rsqrt(double d) {
   return r;
 }
 
+// out-of-line so that the pivot chain's code stays small (never taken for sane systems)
+__device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
+
 // 32x32 lower Cholesky by one warp: lane r holds row r in registers (a[c], c <= r meaningful).
 // Returns the reciprocal pivots through dinv[] (shared) and sets *bad on a non-positive pivot.
-__device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *dinv, int *bad) {
-  const unsigned full = 0xffffffffu;
+// Column j travels between the lanes through `col` (32 doubles of shared memory), one round trip
+// per pivot: every lane publishes its entry of column j, reads the pivot, and updates its row
+// with a[c] -= (a[j]/d) * A[c][j].  (A 64-bit __shfl_sync costs ~12 SASS instructions; the
+// shuffle version of this routine was 8k instructions and the kernel 300 KB, far beyond the
+// instruction cache, which made every panel run at cold-cache speed.)
+__device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *col, double *dinv,
+                                            int *bad) {
 #pragma unroll
   for (int j = 0; j < kPB; j++) {
-    const double d = __shfl_sync(full, a[j], j);
+    __syncwarp();  // previous readers of col are done
+    col[lane] = a[j];
+    __syncwarp();
+    const double d = col[j];
     double r;
     if (!(d > 0.0)) {
       if (lane == 0) *bad = 1;
       r = 1.0;  // keep finite; the step is discarded
+    } else if (d < 1e-30 || d > 1e30) {
+      r = rsqrt_wide_range(d);
     } else {
       r = chain_rsqrt(d);
     }
     if (lane == 0) dinv[j] = r;
-    const double l = a[j] * r;  // lane j: d * rsqrt(d) = sqrt(d); lanes > j: L[lane][j]
-    a[j] = l;
+    const double tj = a[j] * (r * r);  // A[lane][j] / d
+    a[j] *= r;                         // lane j: sqrt(d); lanes > j: L[lane][j]
 #pragma unroll
-    for (int c = j + 1; c < kPB; c++) {
-      const double lc = __shfl_sync(full, l, c);  // L[c][j]
-      a[c] -= l * lc;                             // meaningful for lanes >= c
-    }
+    for (int c = j + 1; c < kPB; c++) a[c] -= tj * col[c];  // meaningful for lanes >= c
   }
 }
 
@@ -119,6 +140,25 @@ __device__ __forceinline__ void tile_from_index(int tile, int &tr, int &tc) {
   tc = tile - tr * (tr + 1) / 2;
 }
 
+constexpr int kLs = kPB + 2;  // even leading dimension: 16-byte aligned pairs for LDS.128
+struct CoopSmem {
+  double L11[kPB][kPB + 1];
+  double Ad[kPB][kPB + 1];   // diagonal block with the previous panel's update folded in
+  double Ls[kPB][kLs];       // previous panel's L21, rows of the diagonal block
+  double dinv[kPB], yk[kPB], bk[kPB], col[kPB];
+  union {
+    struct {
+      double Xr[kTrsmRows][kPB + 1];  // this CTA's rows of the panel
+      double Lp[kTrsmRows][kLs];      // their L21 of the previous panel
+    } a;
+    struct {
+      double Ra[64][kPB + 1], Rb[64][kPB + 1];  // phase B tiles
+    } b;
+  } u;
+  int bad;
+};
+constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
+
 __global__ void __launch_bounds__(kCoopThreads)
     gn_chol_solve_coop_kernel(double *__restrict__ sys, double *__restrict__ ldiag, int D,
                               double *__restrict__ xbuf, float *__restrict__ Twc,
@@ -126,11 +166,12 @@ __global__ void __launch_bounds__(kCoopThreads)
                               int *__restrict__ flags) {
   cg::grid_group grid = cg::this_grid();
   if (flags[0]) return;  // uniform over the grid (the flag only changes after the last barrier)
-  __shared__ double L11[kPB][kPB + 1];
-  __shared__ double dinv[kPB];
-  __shared__ double yk[kPB];
-  __shared__ double Ra[64][kPB + 1], Rb[64][kPB + 1];
-  __shared__ int bad;
+  extern __shared__ __align__(16) unsigned char coop_smem_raw[];
+  CoopSmem &S = *reinterpret_cast<CoopSmem *>(coop_smem_raw);
+  double (*Ra)[kPB + 1] = S.u.b.Ra;
+  double (*Rb)[kPB + 1] = S.u.b.Rb;
+  double *yk = S.yk;
+  int &bad = S.bad;
   const int t = threadIdx.x;
   const int lane = t & 31, warp = t >> 5;
   double *A = sys;
@@ -138,104 +179,172 @@ __global__ void __launch_bounds__(kCoopThreads)
   if (t == 0) bad = 0;
   long long prof_acc[6] = {0, 0, 0, 0, 0, 0};
   long long prof_t = clock64();
+  long long aprof[6] = {0, 0, 0, 0, 0, 0};
+  long long aprof_t = 0;
   __syncthreads();
+  // warp roles in phase A: 0 = POTRF (alone on its scheduler: warp 4 idles), 1,2,3,6 = the
+  // CTA's 128 panel rows (look-ahead update, TRSM, rhs), 5 = forward-substitution chain y_k
+  const bool trsm_warp = (warp >= 1 && warp <= 3) || warp == 6;
+  const int trsm_slot = (warp == 6) ? 3 : warp - 1;
 
   for (int k0 = 0; k0 < D; k0 += kPB) {
     const int pb = min(kPB, D - k0);
     const int m = D - k0 - pb;  // rows below the panel
     const int row_ctas = max(1, (m + kTrsmRows - 1) / kTrsmRows);
-    // ---------------- phase A
+    // Look-ahead: the trailing update of the PREVIOUS panel (columns kp..kp+31) has not been
+    // applied to this panel's columns yet; the panel CTAs fold it into their loads, while the
+    // other CTAs apply it to the rest of the trailing matrix (phase B below) at the same time.
+    const bool la = k0 > 0;
+    const int kp = k0 - kPB;
+    // ---------------- phase A (panel CTAs)
     for (int rc = blockIdx.x; rc < row_ctas; rc += gridDim.x) {
-      // panel rows of this CTA start loading while warp 0 factors the diagonal block
-      const int row = k0 + pb + rc * kTrsmRows + (t - 32);
-      const bool has_row = (warp >= 1 && warp <= kTrsmRows / 32) && row < D;
-      double x[kPB];
-      double *Ar = A + static_cast<size_t>(has_row ? row : 0) * D + k0;
-      if (has_row) {
-#pragma unroll
-        for (int c = 0; c < kPB; c++) x[c] = (c < pb) ? Ar[c] : 0.0;
+      if (blockIdx.x == 0 && t == 0) aprof_t = clock64();
+      const int row0 = k0 + pb + rc * kTrsmRows;
+      const int nrows = max(0, min(kTrsmRows, D - row0));
+      // 1. every operand of the panel step in one round of coalesced loads
+      for (int x = t; x < kPB * kPB; x += kCoopThreads) {
+        const int r = x / kPB, c = x % kPB;
+        const size_t g = static_cast<size_t>(k0 + r) * D;
+        double v = (r >= pb && r == c) ? 1.0 : 0.0;  // identity on the padding of the last panel
+        if (r < pb && c <= r) v = A[g + k0 + c];
+        S.Ad[r][c] = v;
+        S.Ls[r][c] = (la && r < pb) ? A[g + kp + c] : 0.0;
       }
+      for (int x = t; x < kTrsmRows * kPB; x += kCoopThreads) {
+        const int r = x / kPB, c = x % kPB;
+        const size_t g = static_cast<size_t>(row0 + r) * D;
+        S.u.a.Xr[r][c] = (r < nrows && c < pb) ? A[g + k0 + c] : 0.0;
+        S.u.a.Lp[r][c] = (la && r < nrows) ? A[g + kp + c] : 0.0;
+      }
+      if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
+      __syncthreads();
+      COOP_ATICK(8);
+      // 2. diagonal block -= Ls Ls^T (all threads, 4 entries each; entries above the diagonal
+      //    receive garbage and are never read)
+      if (la) {
+        const int r = t >> 3, c0 = (t & 7) * 4;
+        double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma unroll 8
+        for (int j = 0; j < kPB; j++) {
+          const double lr = S.Ls[r][j];
+          s0 += lr * S.Ls[c0][j], s1 += lr * S.Ls[c0 + 1][j];
+          s2 += lr * S.Ls[c0 + 2][j], s3 += lr * S.Ls[c0 + 3][j];
+        }
+        S.Ad[r][c0] -= s0, S.Ad[r][c0 + 1] -= s1, S.Ad[r][c0 + 2] -= s2, S.Ad[r][c0 + 3] -= s3;
+      }
+      __syncthreads();
+      COOP_ATICK(9);
       if (warp == 0) {
+        // 3. POTRF (rows in registers, shuffles)
         double a[kPB];
 #pragma unroll
-        for (int c = 0; c < kPB; c++)
-          a[c] = (lane < pb && c <= lane) ? A[static_cast<size_t>(k0 + lane) * D + (k0 + c)]
-                                          : ((lane >= pb && c == lane) ? 1.0 : 0.0);
-        const double b_mine = (lane < pb) ? rhs[k0 + lane] : 0.0;  // in flight during the factor
-        warp_chol32(a, lane, dinv, &bad);
+        for (int c = 0; c < kPB; c++) a[c] = (c <= lane) ? S.Ad[lane][c] : 0.0;
+        warp_chol32(a, lane, S.col, S.dinv, &bad);
 #pragma unroll
-        for (int c = 0; c < kPB; c++) L11[lane][c] = (c <= lane) ? a[c] : 0.0;
+        for (int c = 0; c < kPB; c++) S.L11[lane][c] = (c <= lane) ? a[c] : 0.0;
         __syncwarp();
-        // release the TRSM warps; the y_k chain below overlaps with their work
-        asm volatile("bar.arrive 1, %0;" ::"r"(kCoopThreads));
-        // y_k = L11^-1 b_k (serial chain over the pivots)
-        double mine = b_mine;
+        asm volatile("bar.arrive 1, 192;");  // L11, dinv ready: TRSM warps and the y_k warp go
+        COOP_ATICK(10);
+      } else if (trsm_warp) {
+        // 4. this thread's row: fold in the previous panel's update while warp 0 factors
+        const int r = trsm_slot * 32 + lane;
+        const int row = row0 + r;
+        const bool has_row = r < nrows;
+        double x[kPB];
+#pragma unroll
+        for (int c = 0; c < kPB; c++) x[c] = S.u.a.Xr[r][c];
+        if (la) {
+#pragma unroll 2
+          for (int j = 0; j < kPB; j += 2) {
+            const double2 lp = *reinterpret_cast<const double2 *>(&S.u.a.Lp[r][j]);
+#pragma unroll
+            for (int c = 0; c < kPB; c++) {
+              const double2 b2 = *reinterpret_cast<const double2 *>(&S.Ls[c][j]);
+              x[c] -= lp.x * b2.x + lp.y * b2.y;
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 192;");
+        // right-looking TRSM: independent updates per column -> ILP
 #pragma unroll
         for (int c = 0; c < kPB; c++) {
-          double yc = (lane == c) ? mine * dinv[c] : 0.0;
-          yc = __shfl_sync(0xffffffffu, yc, c);
-          if (lane == c) mine = yc;
-          else if (lane > c) mine -= a[c] * yc;
+          const double xc = x[c] * S.dinv[c];
+          x[c] = xc;
+#pragma unroll
+          for (int k = c + 1; k < kPB; k++) x[k] -= xc * S.L11[k][c];
         }
-        yk[lane] = (lane < pb) ? mine : 0.0;
+        if (has_row) {
+          double *Ar = A + static_cast<size_t>(row) * D + k0;
+#pragma unroll
+          for (int c = 0; c < kPB; c++)
+            if (c < pb) Ar[c] = x[c];
+        }
+        asm volatile("bar.sync 2, 160;");  // y_k ready
+        if (has_row) {
+          double dot = 0.0;
+#pragma unroll
+          for (int c = 0; c < kPB; c++) dot += x[c] * yk[c];
+          rhs[row] -= dot;
+        }
+      } else if (warp == 5) {
+        // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp
+        asm volatile("bar.sync 1, 192;");
+        double a[kPB];
+#pragma unroll
+        for (int c = 0; c < kPB; c++) a[c] = S.L11[lane][c];
+        double mine = S.bk[lane];
+#pragma unroll
+        for (int c = 0; c < kPB; c++) {  // y_c travels through shared memory (see warp_chol32)
+          if (lane == c) mine *= S.dinv[c], yk[c] = mine;
+          __syncwarp();
+          if (lane > c) mine -= a[c] * yk[c];
+        }
+        __syncwarp();
+        if (lane >= pb) yk[lane] = 0.0;
+        asm volatile("bar.sync 2, 160;");
         if (rc == 0) {
           if (lane < pb) xbuf[k0 + lane] = mine;
           double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
 #pragma unroll
-          for (int c = 0; c < kPB; c++) Ld[lane * kPB + c] = (c <= lane) ? a[c] : 0.0;
-          Ld[kPB * kPB + lane] = dinv[lane];
+          for (int c = 0; c < kPB; c++) Ld[lane * kPB + c] = a[c];
+          Ld[kPB * kPB + lane] = S.dinv[lane];
         }
-      } else {
-        asm volatile("bar.sync 1, %0;" ::"r"(kCoopThreads));  // L11, dinv ready
-      }
-      if (has_row) {  // right-looking TRSM: independent updates per column -> ILP
-#pragma unroll
-        for (int c = 0; c < kPB; c++) {
-          const double xc = x[c] * dinv[c];
-          x[c] = xc;
-#pragma unroll
-          for (int k = c + 1; k < kPB; k++) x[k] -= xc * L11[k][c];
-        }
-#pragma unroll
-        for (int c = 0; c < kPB; c++)
-          if (c < pb) Ar[c] = x[c];
-      }
-      __syncthreads();  // y_k ready
-      if (has_row) {
-        double dot = 0.0;
-#pragma unroll
-        for (int c = 0; c < kPB; c++) dot += x[c] * yk[c];
-        rhs[row] -= dot;
       }
       __syncthreads();
+      COOP_ATICK(13);
     }
     COOP_TICK(0);
-    grid.sync();
-    COOP_TICK(1);
-    // ---------------- phase B
-    if (m > 0) {
+    // ---------------- phase B: A22 -= L21 L21^T of the previous panel on rows/cols >= k0 + pb,
+    // by the CTAs that are not on the panel's critical path (all of them if the grid is small)
+    if (la && m > 0) {
       const int base = k0 + pb;
-      const int T64 = (m + 63) / 64;
-      if (T64 * (T64 + 1) / 2 >= 2 * static_cast<int>(gridDim.x)) {
-        const int ntiles = T64 * (T64 + 1) / 2;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-          int tr, tc;
-          tile_from_index(tile, tr, tc);
-          coop_update_tile<64>(A, D, k0, pb, base, tr, tc, Ra, Rb, t);
-        }
-      } else {  // few tiles: 32x32 tiles spread the update over more SMs
-        const int T32 = (m + 31) / 32;
-        const int ntiles = T32 * (T32 + 1) / 2;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-          int tr, tc;
-          tile_from_index(tile, tr, tc);
-          coop_update_tile<32>(A, D, k0, pb, base, tr, tc, Ra, Rb, t);
+      const int nu = static_cast<int>(gridDim.x) > row_ctas ? static_cast<int>(gridDim.x) - row_ctas
+                                                            : static_cast<int>(gridDim.x);
+      const int u = static_cast<int>(gridDim.x) > row_ctas ? static_cast<int>(blockIdx.x) - row_ctas
+                                                           : static_cast<int>(blockIdx.x);
+      if (u >= 0) {
+        const int T64 = (m + 63) / 64;
+        if (T64 * (T64 + 1) / 2 >= 2 * nu) {
+          const int ntiles = T64 * (T64 + 1) / 2;
+          for (int tile = u; tile < ntiles; tile += nu) {
+            int tr, tc;
+            tile_from_index(tile, tr, tc);
+            coop_update_tile<64>(A, D, kp, kPB, base, tr, tc, Ra, Rb, t);
+          }
+        } else {  // few tiles: 32x32 tiles spread the update over more SMs
+          const int T32 = (m + 31) / 32;
+          const int ntiles = T32 * (T32 + 1) / 2;
+          for (int tile = u; tile < ntiles; tile += nu) {
+            int tr, tc;
+            tile_from_index(tile, tr, tc);
+            coop_update_tile<32>(A, D, kp, kPB, base, tr, tc, Ra, Rb, t);
+          }
         }
       }
-      COOP_TICK(2);
-      grid.sync();
-      COOP_TICK(3);
     }
+    COOP_TICK(2);
+    grid.sync();
+    COOP_TICK(1);
   }
   if (blockIdx.x != 0) return;
 
@@ -254,15 +363,12 @@ __global__ void __launch_bounds__(kCoopThreads)
         const double my_dinv = Ld[kPB * kPB + lane];
         double mine = (lane < pb) ? xbuf[k0 + lane] : 0.0;
 #pragma unroll
-        for (int cc = kPB - 1; cc >= 0; cc--) {
-          double xc = (lane == cc) ? mine * my_dinv : 0.0;
-          xc = __shfl_sync(0xffffffffu, xc, cc);
-          if (cc < pb) {
-            if (lane == cc) mine = xc;
-            else if (lane < cc) mine -= col[cc] * xc;
-          }
+        for (int cc = kPB - 1; cc >= 0; cc--) {  // x_cc travels through shared memory
+          if (lane == cc) mine *= my_dinv, yk[cc] = mine;
+          __syncwarp();
+          if (lane < cc) mine -= col[cc] * yk[cc];
         }
-        yk[lane] = (lane < pb) ? mine : 0.0;
+        __syncwarp();
         if (lane < pb) xbuf[k0 + lane] = mine;
       }
       __syncthreads();
@@ -285,6 +391,7 @@ __global__ void __launch_bounds__(kCoopThreads)
   COOP_TICK(5);
   if (t == 0) {
     for (int k = 0; k < 6; k++) g_coop_prof[k] += prof_acc[k];
+    for (int k = 0; k < 6; k++) g_coop_prof[8 + k] += aprof[k];
     g_coop_prof[6] += 1;
   }
 }

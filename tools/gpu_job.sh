@@ -1,6 +1,3 @@
 set -x
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
-python bench.py > gpurun_out/bench_r1b.json 2> gpurun_out/bench_r1b.err; echo "bench rc=$?"
-B="python bench.py --steps 3 --warmup 3 --skip-cpu --skip-refcuda --profile"
-$B > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches_r1b.csv $B > gpurun_out/ncu_l.log 2>&1
-echo "launchlist rc=$?"
+timeout 900 python -m pytest tests/test_gn_gpu.py -m gpu -x -q > gpurun_out/pytest_gn.log 2>&1; echo "pytest rc=$?"
+timeout 300 python tools/kbench.py coop > gpurun_out/coop.log 2>&1; echo "rc=$?"

@@ -49,15 +49,17 @@ def coop_profile():
     from mast3r_slam_backends import _lib
     D = synth.GN_DEFAULTS
     g = bench.make_gn_graph(int(os.environ.get("KF", 64)), "cuda")
-    out = (ctypes.c_longlong * 8)()
+    out = (ctypes.c_longlong * 16)()
     _lib.lib.m3r_debug_coop_profile(out)
     r = bench.time_gn(g, D, "rays", 0, 1, reps=1)
     _lib.lib.m3r_debug_coop_profile(out)
     n = max(out[6], 1)
-    names = ["phaseA", "sync1", "phaseB", "sync2", "backward", "finish"]
+    names = ["phaseA", "sync1", "phaseB", "sync2", "backward", "finish", "launches", "-", "A:loads", "A:diag update",
+             "A:potrf", "-", "-", "A:trsm+rhs (to CTA barrier)"]
     print(f"coop solver: {out[6]} launches, solve_ms {r['solve_ms']:.3f}, linearize_ms {r['linearize_ms']:.3f}")
     for k, nm in enumerate(names):
-        print(f"  {nm:9s} {out[k] / n / 1.965e3:8.1f} us per launch")
+        if nm not in ("launches", "-"):
+            print(f"  {nm:18s} {out[k] / n / 1.965e3:8.1f} us per launch")
 
 
 if __name__ == "__main__" and "coop" in sys.argv:

@@ -74,6 +74,22 @@ __device__ __noinline__ void cholB(double (*S)[kPB + 1], int lane, double *dinv)
     __syncwarp();
   }
 }
+// D: rows in registers, column j broadcast through shared memory, one round trip per pivot
+__device__ __forceinline__ void cholD(double a[kPB], int lane, double *col, double *dinv) {
+#pragma unroll
+  for (int j = 0; j < kPB; j++) {
+    __syncwarp();
+    col[lane] = a[j];
+    __syncwarp();
+    const double d = col[j];
+    const double r = chain_rsqrt(d);
+    if (lane == 0) dinv[j] = r;
+    const double tj = a[j] * (r * r);
+    a[j] *= r;
+#pragma unroll
+    for (int c = j + 1; c < kPB; c++) a[c] -= tj * col[c];
+  }
+}
 template <int V>
 __global__ void k(const double *A, double *out, long long *cyc, int reps) {
   __shared__ double S[kPB][kPB + 1];
@@ -91,6 +107,7 @@ __global__ void k(const double *A, double *out, long long *cyc, int reps) {
     if (V == 0) cholA(a, lane, dinv);
     if (V == 1) cholB(S, lane, dinv);
     if (V == 2) cholC(a, lane, dinv);
+    if (V == 3) cholD(a, lane, S[0], dinv);
     const long long t1 = clock64();
     if (lane == 0) cyc[rep] = t1 - t0;
     if (V == 1) {
@@ -109,11 +126,13 @@ int main() {
   cudaMalloc(&dA, sizeof(h)); cudaMalloc(&dO, sizeof(h)); cudaMalloc(&dc, 64);
   cudaMemcpy(dA, h, sizeof(h), cudaMemcpyHostToDevice);
   double ref[kPB * kPB];
-  const char *names[] = {"A registers+rsqrt chain", "B shared memory rolled", "C registers LDL^T chain"};
-  for (int v = 0; v < 3; v++) {
+  const char *names[] = {"A registers+rsqrt chain", "B shared memory rolled", "C registers LDL^T chain",
+                         "D registers + smem broadcast"};
+  for (int v = 0; v < 4; v++) {
     if (v == 0) k<0><<<1, 32>>>(dA, dO, dc, 4);
     if (v == 1) k<1><<<1, 32>>>(dA, dO, dc, 4);
     if (v == 2) k<2><<<1, 32>>>(dA, dO, dc, 4);
+    if (v == 3) k<3><<<1, 32>>>(dA, dO, dc, 4);
     cudaMemcpy(hc, dc, 32, cudaMemcpyDeviceToHost);
     cudaMemcpy(o, dO, sizeof(o), cudaMemcpyDeviceToHost);
     if (v == 0) for (int i = 0; i < kPB * kPB; i++) ref[i] = o[i];
