@@ -136,7 +136,55 @@ def make_match_sets(device, num_sets, seed0=0):
         rays, pts, p0 = synth.prep_for_iter_proj(m["X11"], m["X21"])
         sets.append(dict(rays=rays, pts=pts, p_init=p0, D11=m["D11"].half().contiguous(),
                          D21=m["D21"].view(1, N_PTS, FDIM).half().contiguous()))
+        if s < 4:  # raw pointmaps for the whole-front-end timing (time_front_end)
+            FRONT_INPUTS.append((m["X11"].contiguous(), m["X21"].contiguous()))
     return sets
+
+
+FRONT_INPUTS = []
+
+
+def time_front_end(be, sets, M, steps, warmup):
+    """mast3r_slam/matching.py::match as a whole (SURVEY.md 8f rows N1+N3), inputs resident:
+    the fused C-ABI call (3 launches) next to the reference-shaped sequence -- the torch glue of
+    matching.py:25-88 around this library's two kernels."""
+    import synth
+    from mast3r_slam_backends import matching as front
+
+    front.set_config({"matching": dict(M)})
+
+    def fused(i):
+        X11, X21 = FRONT_INPUTS[i % len(FRONT_INPUTS)]
+        s = sets[i % len(FRONT_INPUTS)]
+        return front.match(X11, X21, s["D11"], s["D21"])
+
+    def unfused(i):
+        X11, X21 = FRONT_INPUTS[i % len(FRONT_INPUTS)]
+        s = sets[i % len(FRONT_INPUTS)]
+        rays, pts, p0 = synth.prep_for_iter_proj(X11, X21)
+        p, conv = be.iter_proj(rays, pts, p0, M["max_iter"], M["lambda_init"], M["convergence_thresh"])
+        p1 = p.long()
+        bi = torch.arange(1, device=X11.device)[:, None].repeat(1, N_PTS)
+        d = torch.linalg.norm(X11[bi, p1[..., 1], p1[..., 0], :].reshape(1, H, W, 3) - X21, dim=-1)
+        valid = conv & (d < M["dist_thresh"]).view(1, -1)
+        (p1n,) = be.refine_matches(s["D11"].half(), s["D21"].half(), p1, M["radius"], M["dilation_max"])
+        return p1n[..., 0] + W * p1n[..., 1], valid.unsqueeze(-1)
+
+    out = {}
+    for name, fn in (("fused_ms", fused), ("torch_glue_ms", unfused)):
+        for i in range(warmup):
+            fn(i)
+        torch.cuda.synchronize()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for i in range(steps):
+            fn(i)
+        t1.record()
+        torch.cuda.synchronize()
+        out[name] = t0.elapsed_time(t1) / steps
+    out["fused_launches"] = 3
+    out["fused_px_per_s"] = N_PTS / (out["fused_ms"] * 1e-3)
+    return out
 
 
 def match_step(be, s, M):
@@ -491,6 +539,9 @@ def main():
                     "iter_proj_gbs": iproj_gbs, "iter_proj_frac": iproj_gbs / peak,
                     "pair_gbs": pair_gbs, "pair_frac": pair_gbs / peak},
     }
+
+    if rank == 0 and not args.profile:
+        line["front_end"] = time_front_end(be, sets, M, max(args.steps // 4, 10), 3)
 
     # ---- Gauss-Newton
     g = None

@@ -91,6 +91,37 @@ int m3r_refine_matches_v(const void *D11, const void *D21, const int64_t *p1, in
                          int dilation_max, int variant, void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Matching front end -- the torch code either side of the two kernels above, fused
+ * (SURVEY.md 8f rows N1 and N3).
+ *
+ * m3r_prep_rays replaces the ray-image part of `prep_for_iter_proj(X11, X21,
+ * idx_1_to_2_init)` (mast3r_slam/matching.py:25-36) and `img_gradient(img)`
+ * (mast3r_slam/image.py:5-38): F.normalize over xyz (eps 1e-12), the two depthwise 3x3
+ * filters on the reflect-padded ray image, and the concat/permute into iter_proj's layout.
+ *   X11                [b,h,w,3] f32   canonical pointmap of view 1
+ *   rays_img_with_grad [b,h,w,9] f32   out
+ *
+ * m3r_match replaces `match(X11, X21, D11, D21, idx_1_to_2_init) -> (idx_1_to_2,
+ * valid_match2)` (matching.py:8-10, 52-88): prep, iter_proj, `.long()`, the 3D-distance
+ * occlusion test, refine_matches (when radius > 0) and pixel_to_lin, in three launches.
+ *   X21        [b,h,w,3]    f32    view-2 points in view 1's frame (n = h*w queries)
+ *   D11, D21   [b,h,w,fdim] dtype  descriptors, ALREADY in the dtype the reference would
+ *                                  refine in (it casts to half: matching.py:79-80); may be
+ *                                  NULL when radius == 0
+ *   idx_init   [b,n] i64 or NULL   previous idx_1_to_2 (NULL = identity, matching.py:41-44)
+ *   idx_1_to_2 [b,n] i64           out: u + w*v of the refined pixel
+ *   valid      [b,n] u8            out: converged && |X11[p1] - X21| < dist_thresh
+ *   rays_ws    b*h*w*9 floats      caller-owned scratch (holds rays_img_with_grad on return)
+ *   p1_ws      2*b*n*2 int64       caller-owned scratch, 16-byte aligned
+ * ------------------------------------------------------------------------------------- */
+int m3r_prep_rays(const float *X11, float *rays_img_with_grad, int b, int h, int w, void *stream);
+int m3r_match(const float *X11, const float *X21, const void *D11, const void *D21, int fdim,
+              int dtype, const int64_t *idx_init, int64_t *idx_1_to_2, uint8_t *valid,
+              float *rays_ws, int64_t *p1_ws, int b, int h, int w, int max_iter,
+              float lambda_init, float cost_thresh, float dist_thresh, int radius,
+              int dilation_max, void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * Gauss-Newton on the Sim(3) keyframe graph.
  *
  * A workspace caches device scratch (per-edge blocks, the assembled system, index maps)

@@ -109,6 +109,50 @@ __device__ __forceinline__ void lm_step(const float gx[3], const float gy[3], co
   v_new = clampf(v + delta_v, 1.0f, v_hi);
 }
 
+// The memoised LM loop (MODE 0 of iter_proj_kernel, see below), shared with the fused match
+// kernel.
+__device__ __forceinline__ void iter_proj_memo(const GlobalFetch &fetch, const float pt[3], float &u,
+                                               float &v, float u_hi, float v_hi, int max_iter,
+                                               float lambda_init, float cost_thresh, bool &conv) {
+  auto f9 = [&](int uu, int vv, float *out) { fetch.template operator()<9>(uu, vv, out); };
+  float lambda = lambda_init;
+  conv = false;
+  if (max_iter <= 0) return;
+  float gx[3], gy[3], err[3], cost;
+  eval_at<true>(f9, u, v, pt, gx, gy, err, cost);
+  float ut = 0.f, vt = 0.f, cost_t = 0.f;  // last rejected trial since the pixel last moved
+  bool have_trial = false;
+  for (int it = 0; it < max_iter; it++) {
+    float u_new, v_new;
+    lm_step(gx, gy, err, lambda, u, v, u_hi, v_hi, u_new, v_new);
+    float ngx[3], ngy[3], nerr[3], new_cost;
+    bool fresh = false;
+    if (u_new == u && v_new == v) {
+      new_cost = cost;
+    } else if (have_trial && u_new == ut && v_new == vt) {
+      new_cost = cost_t;
+    } else {
+      eval_at<true>(f9, u_new, v_new, pt, ngx, ngy, nerr, new_cost);
+      fresh = true;
+    }
+    // a memoised cost is never below `cost` (it was rejected against the same `cost`)
+    if (fresh && new_cost < cost) {
+      u = u_new;
+      v = v_new;
+      cost = new_cost;
+#pragma unroll
+      for (int j = 0; j < 3; j++) gx[j] = ngx[j], gy[j] = ngy[j], err[j] = nerr[j];
+      have_trial = false;
+      lambda = static_cast<float>(static_cast<double>(lambda) * 0.1);
+      conv = new_cost < cost_thresh;
+    } else {
+      ut = u_new, vt = v_new, cost_t = new_cost, have_trial = true;
+      lambda = lambda * 10.0f;
+      conv = cost < cost_thresh;
+    }
+  }
+}
+
 constexpr int kIpThreads = 128;
 
 // MODE 1: every iteration evaluates the current pixel (9 channels) and the trial pixel
@@ -163,43 +207,98 @@ __global__ void __launch_bounds__(kIpThreads)
         conv = cost < cost_thresh;
       }
     }
-  } else if (max_iter > 0) {
-    float gx[3], gy[3], err[3], cost;
-    eval_at<true>(f9, u, v, pt, gx, gy, err, cost);
-    float ut = 0.f, vt = 0.f, cost_t = 0.f;  // last rejected trial since the pixel last moved
-    bool have_trial = false;
-    for (int it = 0; it < max_iter; it++) {
-      float u_new, v_new;
-      lm_step(gx, gy, err, lambda, u, v, u_hi, v_hi, u_new, v_new);
-      float ngx[3], ngy[3], nerr[3], new_cost;
-      bool fresh = false;
-      if (u_new == u && v_new == v) {
-        new_cost = cost;
-      } else if (have_trial && u_new == ut && v_new == vt) {
-        new_cost = cost_t;
-      } else {
-        eval_at<true>(f9, u_new, v_new, pt, ngx, ngy, nerr, new_cost);
-        fresh = true;
-      }
-      // a memoised cost is never below `cost` (it was rejected against the same `cost`)
-      if (fresh && new_cost < cost) {
-        u = u_new;
-        v = v_new;
-        cost = new_cost;
-#pragma unroll
-        for (int j = 0; j < 3; j++) gx[j] = ngx[j], gy[j] = ngy[j], err[j] = nerr[j];
-        have_trial = false;
-        lambda = static_cast<float>(static_cast<double>(lambda) * 0.1);
-        conv = new_cost < cost_thresh;
-      } else {
-        ut = u_new, vt = v_new, cost_t = new_cost, have_trial = true;
-        lambda = lambda * 10.0f;
-        conv = cost < cost_thresh;
-      }
-    }
+  } else {
+    iter_proj_memo(fetch, pt, u, v, u_hi, v_hi, max_iter, lambda_init, cost_thresh, conv);
   }
   reinterpret_cast<float2 *>(p_new)[gi] = make_float2(u, v);
   converged[gi] = conv ? 1 : 0;
+}
+
+// =========================================================================================
+// fused matching front end (callers: mast3r_slam/matching.py)
+// =========================================================================================
+//
+// prep_rays: `prep_for_iter_proj` + `img_gradient` (matching.py:25-36, image.py:5-38) in one
+// pass: rays = X / max(|X|, 1e-12) (F.normalize), gx/gy = the reference's 3x3 taps
+// (1/32)[-3 0 3; -10 0 10; -3 0 3] and its transpose on the reflect-padded ray image, written
+// straight in the [b,h,w,9] layout iter_proj reads.  The reference runs ~8 torch kernels and
+// moves about 10x the bytes of the result for this.
+constexpr int kPrTx = 32, kPrTy = 8;
+
+__device__ __forceinline__ int reflect_idx(int i, int n) {  // F.pad(mode="reflect"), pad 1
+  return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
+}
+
+__global__ void __launch_bounds__(kPrTx * kPrTy)
+    prep_rays_kernel(const float *__restrict__ X11, float *__restrict__ rays, int h, int w) {
+  __shared__ float tile[kPrTy + 2][kPrTx + 2][3];
+  const int b = blockIdx.z;
+  const int u0 = blockIdx.x * kPrTx, v0 = blockIdx.y * kPrTy;
+  const float *img = X11 + static_cast<size_t>(b) * h * w * 3;
+  for (int x = threadIdx.x; x < (kPrTy + 2) * (kPrTx + 2); x += kPrTx * kPrTy) {
+    const int ty = x / (kPrTx + 2), tx = x - ty * (kPrTx + 2);
+    const int vv = reflect_idx(min(v0 + ty - 1, h), h), uu = reflect_idx(min(u0 + tx - 1, w), w);
+    const float *p = img + (static_cast<size_t>(min(vv, h - 1)) * w + min(uu, w - 1)) * 3;
+    const float X = __ldg(p), Y = __ldg(p + 1), Z = __ldg(p + 2);
+    const float d = fmaxf(sqrtf(X * X + Y * Y + Z * Z), 1e-12f);
+    tile[ty][tx][0] = X / d, tile[ty][tx][1] = Y / d, tile[ty][tx][2] = Z / d;
+  }
+  __syncthreads();
+  const int tx = threadIdx.x % kPrTx, ty = threadIdx.x / kPrTx;
+  const int u = u0 + tx, v = v0 + ty;
+  if (u >= w || v >= h) return;
+  float out[9];
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    const float a00 = tile[ty][tx][c], a01 = tile[ty][tx + 1][c], a02 = tile[ty][tx + 2][c];
+    const float a10 = tile[ty + 1][tx][c], a11 = tile[ty + 1][tx + 1][c], a12 = tile[ty + 1][tx + 2][c];
+    const float a20 = tile[ty + 2][tx][c], a21 = tile[ty + 2][tx + 1][c], a22 = tile[ty + 2][tx + 2][c];
+    out[c] = a11;
+    out[3 + c] = 0.09375f * (a02 - a00) + 0.3125f * (a12 - a10) + 0.09375f * (a22 - a20);
+    out[6 + c] = 0.09375f * (a20 - a00) + 0.3125f * (a21 - a01) + 0.09375f * (a22 - a02);
+  }
+  float *dst = rays + ((static_cast<size_t>(b) * h + v) * w + u) * 9;
+#pragma unroll
+  for (int c = 0; c < 9; c++) dst[c] = out[c];
+}
+
+// match_proj: iter_proj with its torch prologue and epilogue folded in (matching.py:38-76):
+// the query ray is normalised here (F.normalize of X21), the initial pixel comes from the
+// previous match index (lin_to_pixel) or the identity, and the result leaves as the truncated
+// integer pixel (`p1.long()`) together with valid = converged & |X11[p1] - X21| < dist_thresh.
+__global__ void __launch_bounds__(kIpThreads)
+    match_proj_kernel(const float *__restrict__ rays, const float *__restrict__ X11,
+                      const float *__restrict__ X21, const long long *__restrict__ idx_init,
+                      long long *__restrict__ p1, uint8_t *__restrict__ valid, int h, int w, int n,
+                      int max_iter, float lambda_init, float cost_thresh, float dist_thresh) {
+  const int b = blockIdx.y;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const size_t gi = static_cast<size_t>(b) * n + idx;
+  const GlobalFetch fetch{rays + static_cast<size_t>(b) * h * w * 9, w};
+  const float X = __ldg(X21 + gi * 3), Y = __ldg(X21 + gi * 3 + 1), Z = __ldg(X21 + gi * 3 + 2);
+  const float d = fmaxf(sqrtf(X * X + Y * Y + Z * Z), 1e-12f);
+  const float pt[3] = {X / d, Y / d, Z / d};
+  const long long lin = idx_init ? idx_init[gi] : static_cast<long long>(idx);
+  const float u_hi = static_cast<float>(w - 2), v_hi = static_cast<float>(h - 2);
+  float u = clampf(static_cast<float>(lin % w), 1.0f, u_hi);
+  float v = clampf(static_cast<float>(lin / w), 1.0f, v_hi);
+  bool conv;
+  iter_proj_memo(fetch, pt, u, v, u_hi, v_hi, max_iter, lambda_init, cost_thresh, conv);
+  const int u1 = static_cast<int>(u), v1 = static_cast<int>(v);  // .long(): truncation, values >= 1
+  const float *q = X11 + ((static_cast<size_t>(b) * h + v1) * w + u1) * 3;
+  const float dx = __ldg(q) - X, dy = __ldg(q + 1) - Y, dz = __ldg(q + 2) - Z;
+  const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
+  reinterpret_cast<longlong2 *>(p1)[gi] = make_longlong2(u1, v1);
+  valid[gi] = (conv && dist < dist_thresh) ? 1 : 0;
+}
+
+__global__ void pixel_to_lin_kernel(const long long *__restrict__ p1, long long *__restrict__ lin,
+                                    long long total, int w) {
+  const long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= total) return;
+  const longlong2 p = reinterpret_cast<const longlong2 *>(p1)[k];
+  lin[k] = p.x + static_cast<long long>(w) * p.y;
 }
 
 // =========================================================================================
@@ -373,7 +472,7 @@ __device__ __forceinline__ __half2 score_pair(const uint4 *ra, const uint4 *rb,
 __global__ void __launch_bounds__(kRtThreads, 2)
     refine_f16_tiled_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
                             const long long *__restrict__ p1, long long *__restrict__ p1_new,
-                            int h, int w, int dilation_max) {
+                            long long *__restrict__ lin_out, int h, int w, int dilation_max) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint4 *tile = reinterpret_cast<uint4 *>(smem_raw);
   unsigned long long *mbar = reinterpret_cast<unsigned long long *>(smem_raw + kRtTileBytes);
@@ -531,8 +630,10 @@ __global__ void __launch_bounds__(kRtThreads, 2)
     v0 = v_new;
   }
   if (active) {
-    reinterpret_cast<longlong2 *>(p1_new)[gi] =
+    const longlong2 res =
         live ? make_longlong2(static_cast<long long>(u_new), static_cast<long long>(v_new)) : p;
+    if (p1_new) reinterpret_cast<longlong2 *>(p1_new)[gi] = res;
+    if (lin_out) lin_out[gi] = res.x + static_cast<long long>(w) * res.y;  // pixel_to_lin (matching.py:88)
   }
 }
 
@@ -620,6 +721,26 @@ __global__ void __launch_bounds__(kRefineThreads)
 // =========================================================================================
 using namespace m3r;
 
+static int launch_refine_tiled(const __half *D11, const __half *D21, const long long *p1,
+                               long long *p1_new, long long *lin_out, int b, int h, int w,
+                               int dilation_max, cudaStream_t s) {
+  static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
+  int dev = 0;
+  M3R_CUDA_TRY(cudaGetDevice(&dev));
+  bool &attr_set = attr_set_dev[dev & 63];
+  if (!attr_set) {
+    M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
+    attr_set = true;
+  }
+  const dim3 tgrid((w + kRtQ - 1) / kRtQ, (h + kRtQ - 1) / kRtQ, b);
+  M3R_REQUIRE(tgrid.y <= 65535, "refine_matches: image too tall");
+  refine_f16_tiled_kernel<<<tgrid, kRtThreads, kRtSmemBytes, s>>>(D11, D21, p1, p1_new, lin_out, h, w,
+                                                                 dilation_max);
+  M3R_LAUNCH_CHECK("refine_f16_tiled_kernel");
+  return M3R_OK;
+}
+
 extern "C" int m3r_iter_proj_v(const float *rays, const float *pts, const float *p_init,
                                float *p_new, uint8_t *converged, int b, int h, int w, int n,
                                int max_iter, float lambda_init, float cost_thresh, int variant,
@@ -678,20 +799,10 @@ extern "C" int m3r_refine_matches_v(const void *D11, const void *D21, const int6
     const bool tiled = fast && variant == 0 && radius == 3 && dilation_max >= 1 &&
                        static_cast<long long>(n) == static_cast<long long>(h) * w;
     if (tiled) {
-      static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
-      int dev = 0;
-      M3R_CUDA_TRY(cudaGetDevice(&dev));
-      bool &attr_set = attr_set_dev[dev & 63];
-      if (!attr_set) {
-        M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
-        attr_set = true;
-      }
-      const dim3 tgrid((w + kRtQ - 1) / kRtQ, (h + kRtQ - 1) / kRtQ, b);
-      M3R_REQUIRE(tgrid.y <= 65535, "refine_matches: image too tall");
-      refine_f16_tiled_kernel<<<tgrid, kRtThreads, kRtSmemBytes, s>>>(
-          static_cast<const __half *>(D11), static_cast<const __half *>(D21), p1l, p1nl, h, w,
-          dilation_max);
+      const int rc = launch_refine_tiled(static_cast<const __half *>(D11), static_cast<const __half *>(D21),
+                                         p1l, p1nl, nullptr, b, h, w, dilation_max, s);
+      if (rc) return rc;
+      return M3R_OK;
     } else if (fast) {
       refine_f16_kernel<24><<<grid, block, 0, s>>>(static_cast<const __half *>(D11),
                                                    static_cast<const __half *>(D21), p1l, p1nl,
@@ -724,4 +835,66 @@ extern "C" int m3r_refine_matches(const void *D11, const void *D21, const int64_
                                   int dtype, int radius, int dilation_max, void *stream) {
   return m3r_refine_matches_v(D11, D21, p1, p1_new, b, h, w, n, fdim, dtype, radius,
                               dilation_max, 0, stream);
+}
+
+// -----------------------------------------------------------------------------------------
+// fused matching front end
+// -----------------------------------------------------------------------------------------
+extern "C" int m3r_prep_rays(const float *X11, float *rays_img_with_grad, int b, int h, int w,
+                             void *stream) {
+  M3R_REQUIRE(b >= 0, "prep_rays: negative batch");
+  if (b == 0) return M3R_OK;
+  M3R_REQUIRE(X11 && rays_img_with_grad, "prep_rays: null pointer");
+  M3R_REQUIRE(h >= 2 && w >= 2, "prep_rays: reflect padding needs at least 2x2 (got %dx%d)", h, w);
+  M3R_REQUIRE(b <= 65535 && (h + kPrTy - 1) / kPrTy <= 65535, "prep_rays: image or batch too large");
+  const dim3 grid((w + kPrTx - 1) / kPrTx, (h + kPrTy - 1) / kPrTy, b);
+  prep_rays_kernel<<<grid, kPrTx * kPrTy, 0, static_cast<cudaStream_t>(stream)>>>(X11, rays_img_with_grad,
+                                                                               h, w);
+  M3R_LAUNCH_CHECK("prep_rays_kernel");
+  return M3R_OK;
+}
+
+extern "C" int m3r_match(const float *X11, const float *X21, const void *D11, const void *D21,
+                         int fdim, int dtype, const int64_t *idx_init, int64_t *idx_1_to_2,
+                         uint8_t *valid, float *rays_ws, int64_t *p1_ws, int b, int h, int w,
+                         int max_iter, float lambda_init, float cost_thresh, float dist_thresh,
+                         int radius, int dilation_max, void *stream) {
+  M3R_REQUIRE(b >= 0, "match: negative batch");
+  if (b == 0) return M3R_OK;
+  M3R_REQUIRE(X11 && X21 && idx_1_to_2 && valid && rays_ws && p1_ws, "match: null pointer");
+  M3R_REQUIRE(h >= 3 && w >= 3, "match: image must be at least 3x3 (got %dx%d)", h, w);
+  M3R_REQUIRE(b <= 65535, "match: batch %d exceeds grid.y limit", b);
+  M3R_REQUIRE(static_cast<long long>(h) * w < (1LL << 31), "match: image too large");
+  M3R_REQUIRE((reinterpret_cast<uintptr_t>(p1_ws) & 15u) == 0, "match: p1_ws must be 16-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int n = h * w;
+  int rc = m3r_prep_rays(X11, rays_ws, b, h, w, stream);
+  if (rc) return rc;
+  long long *p1 = reinterpret_cast<long long *>(p1_ws);
+  long long *p1n = p1 + static_cast<size_t>(b) * n * 2;
+  const dim3 grid((n + kIpThreads - 1) / kIpThreads, b);
+  match_proj_kernel<<<grid, kIpThreads, 0, s>>>(rays_ws, X11, X21,
+                                                reinterpret_cast<const long long *>(idx_init), p1, valid,
+                                                h, w, n, max_iter, lambda_init, cost_thresh, dist_thresh);
+  M3R_LAUNCH_CHECK("match_proj_kernel");
+  const long long total = static_cast<long long>(b) * n;
+  if (radius > 0) {  // matching.py:78
+    M3R_REQUIRE(D11 && D21, "match: null descriptor pointer");
+    const bool tiled = dtype == M3R_DTYPE_F16 && fdim == 24 && radius == 3 && dilation_max >= 1 &&
+                       aligned16(D11) && aligned16(D21);
+    if (tiled) {
+      rc = launch_refine_tiled(static_cast<const __half *>(D11), static_cast<const __half *>(D21), p1,
+                               nullptr, reinterpret_cast<long long *>(idx_1_to_2), b, h, w, dilation_max, s);
+      if (rc) return rc;
+      return M3R_OK;
+    }
+    rc = m3r_refine_matches(D11, D21, p1_ws, reinterpret_cast<int64_t *>(p1n), b, h, w, n, fdim, dtype,
+                            radius, dilation_max, stream);
+    if (rc) return rc;
+    p1 = p1n;
+  }
+  pixel_to_lin_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, s>>>(
+      p1, reinterpret_cast<long long *>(idx_1_to_2), total, w);
+  M3R_LAUNCH_CHECK("pixel_to_lin_kernel");
+  return M3R_OK;
 }

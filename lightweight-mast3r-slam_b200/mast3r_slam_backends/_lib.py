@@ -86,6 +86,12 @@ refine_matches = _sig(
 refine_matches_v = _sig(
     "m3r_refine_matches_v", c_int, [c_void_p] * 4 + [c_int] * 9 + [c_void_p]
 )
+prep_rays = _sig("m3r_prep_rays", c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p])
+match = _sig(
+    "m3r_match",
+    c_int,
+    [c_void_p] * 4 + [c_int] * 2 + [c_void_p] * 5 + [c_int] * 4 + [c_float] * 3 + [c_int] * 2 + [c_void_p],
+)
 
 gn_workspace_create = _sig("m3r_gn_workspace_create", c_int, [ctypes.POINTER(c_void_p)])
 gn_workspace_destroy = _sig("m3r_gn_workspace_destroy", None, [c_void_p])
@@ -142,6 +148,8 @@ EXPORTS = [
     "m3r_iter_proj_v",
     "m3r_refine_matches",
     "m3r_refine_matches_v",
+    "m3r_prep_rays",
+    "m3r_match",
     "m3r_gn_workspace_create",
     "m3r_gn_workspace_destroy",
     "m3r_gauss_newton_rays",

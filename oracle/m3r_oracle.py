@@ -174,3 +174,60 @@ def gauss_newton(params, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_ite
                                           _p(jj), _p(idx), _p(vm), _p(Q), N, n, E, int(max_iter),
                                           ctypes.c_float(delta_thresh), _p(dx))
     return T, dx, iters
+
+
+# --------------------------------------------------------------------------------------------
+# matching front end: CPU restatement of mast3r_slam/matching.py and
+# mast3r_slam/image.py around the two kernels above.  Pinned by tests/golden/front_*.npz,
+# which tests/golden/make_golden_front.py writes by running the reference's own matching.py
+# (imported from /root/reference, its extension module replaced by this oracle's kernels).
+# --------------------------------------------------------------------------------------------
+def img_gradient(img):
+    """image.py:5-38: depthwise 3x3 taps (1/32)[-3 0 3; -10 0 10; -3 0 3] and the transpose,
+    reflect padding.  img is [b,c,h,w]."""
+    import torch.nn.functional as F
+
+    c = img.shape[1]
+    gxk = (1.0 / 32.0) * torch.tensor([[-3.0, 0.0, 3.0], [-10.0, 0.0, 10.0], [-3.0, 0.0, 3.0]],
+                                      dtype=img.dtype)
+    pad = F.pad(img, (1, 1, 1, 1), mode="reflect")
+    gx = F.conv2d(pad, gxk.repeat(c, 1, 1, 1), groups=c)
+    gy = F.conv2d(pad, gxk.T.contiguous().repeat(c, 1, 1, 1), groups=c)
+    return gx, gy
+
+
+def prep_for_iter_proj(X11, X21, idx_1_to_2_init=None):
+    """matching.py:25-49.  Returns (rays_with_grad_img [b,h,w,9], pts3d_norm [b,n,3], p_init)."""
+    import torch.nn.functional as F
+
+    X11, X21 = _cpu(X11, torch.float32), _cpu(X21, torch.float32)
+    b, h, w, _ = X11.shape
+    rays = F.normalize(X11, dim=-1).permute(0, 3, 1, 2)
+    gx, gy = img_gradient(rays)
+    rays_with_grad = torch.cat((rays, gx, gy), dim=1).permute(0, 2, 3, 1).contiguous()
+    pts = F.normalize(X21.reshape(b, -1, 3), dim=-1)
+    if idx_1_to_2_init is None:
+        idx_1_to_2_init = torch.arange(h * w)[None, :].repeat(b, 1)
+    idx0 = _cpu(idx_1_to_2_init, torch.int64)
+    p_init = torch.stack((idx0 % w, idx0 // w), dim=-1).float()  # lin_to_pixel, matching.py:18-22
+    return rays_with_grad, pts, p_init
+
+
+def match(X11, X21, D11, D21, idx_1_to_2_init=None, *, max_iter=10, lambda_init=1e-8,
+          convergence_thresh=1e-6, dist_thresh=0.1, radius=3, dilation_max=5):
+    """matching.py:8-88 (match -> match_iterative_proj).  Returns (idx_1_to_2 [b,n] i64,
+    valid_match2 [b,n,1] bool)."""
+    X11, X21 = _cpu(X11, torch.float32), _cpu(X21, torch.float32)
+    b, h, w = X21.shape[:3]
+    rays, pts, p_init = prep_for_iter_proj(X11, X21, idx_1_to_2_init)
+    p1, valid_proj2 = iter_proj(rays, pts, p_init, max_iter, lambda_init, convergence_thresh)
+    p1 = p1.long()
+    batch_inds = torch.arange(b)[:, None].repeat(1, h * w)
+    dists2 = torch.linalg.norm(X11[batch_inds, p1[..., 1], p1[..., 0], :].reshape(b, h, w, 3) - X21,
+                               dim=-1)
+    valid_proj2 = valid_proj2 & (dists2 < dist_thresh).view(b, -1)
+    if radius > 0:
+        (p1,) = refine_matches(_cpu(D11).half(), _cpu(D21).reshape(b, h * w, -1).half(), p1, radius,
+                               dilation_max)
+    idx_1_to_2 = p1[..., 0] + w * p1[..., 1]  # pixel_to_lin, matching.py:13-15
+    return idx_1_to_2, valid_proj2.unsqueeze(-1)

@@ -1,0 +1,159 @@
+"""GPU parity tests of the fused matching front end: m3r_prep_rays
+and m3r_match through mast3r_slam_backends.matching, against the committed golden vectors
+(the reference's own matching.py / image.py run on CPU, tests/golden/make_golden_front.py) and
+against the CPU oracle on seeded inputs.
+
+Tolerances: the ray image is fp32 arithmetic in a different summation order than
+torch's conv2d -> 2e-6 absolute (values are O(1)); match indices and the valid mask agree on
+>= 99.9 % of pixels (BASELINE.json north_star, same bar as iter_proj: a sub-pixel position
+that lands within rounding of an integer may truncate to the neighbouring pixel)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+
+pytestmark = pytest.mark.gpu
+M = synth.MATCH_DEFAULTS
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RAY_TOL = 2e-6
+
+
+@pytest.fixture(scope="module")
+def front(backends):
+    from mast3r_slam_backends import matching
+
+    matching.set_config({"matching": dict(M)})
+    return matching
+
+
+def _case(h, w, b, seed, init):
+    m = synth.make_match_inputs(h, w, b=b, seed=seed, device="cuda")
+    idx_init = None
+    if init != "identity":
+        tu = m["true_uv"].round().long()
+        if init == "shifted":
+            tu = tu + torch.tensor([3, -2], device="cuda")
+        idx_init = (tu[..., 1].clamp(0, h - 1) * w + tu[..., 0].clamp(0, w - 1)).contiguous()
+    return m, idx_init
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "front_*.npz"))) or [None])
+def test_golden_front_end_gpu(front, path):
+    if path is None:
+        pytest.skip("no golden front-end vectors committed")
+    z = np.load(path)
+    X11, X21 = torch.from_numpy(z["X11"]).cuda(), torch.from_numpy(z["X21"]).cuda()
+    D11 = torch.from_numpy(z["D11_f16"]).view(torch.float16).cuda()
+    D21 = torch.from_numpy(z["D21_f16"]).view(torch.float16).cuda()
+    idx_init = torch.from_numpy(z["idx_init"]).cuda() if "idx_init" in z else None
+    rays = front.ray_image_with_grad(X11)
+    err = (rays.cpu() - torch.from_numpy(z["ref_rays"])).abs().max().item()
+    print(f"{os.path.basename(path)}: ray image max abs err {err:.3e}")
+    assert err <= RAY_TOL
+    r2, pts, p0 = front.prep_for_iter_proj(X11, X21, idx_init)
+    assert torch.equal(r2, rays)
+    assert (pts.cpu() - torch.from_numpy(z["ref_pts"])).abs().max() <= 1e-6
+    assert torch.equal(p0.cpu(), torch.from_numpy(z["ref_p_init"]))
+    idx, valid = front.match(X11, X21, D11, D21, idx_init)
+    assert idx.dtype == torch.int64 and valid.dtype == torch.bool
+    assert idx.shape == z["ref_idx"].shape and valid.shape == z["ref_valid"].shape
+    fi = (idx.cpu() == torch.from_numpy(z["ref_idx"])).float().mean().item()
+    fv = (valid.cpu() == torch.from_numpy(z["ref_valid"])).float().mean().item()
+    print(f"{os.path.basename(path)}: idx agreement {fi:.6f}, valid agreement {fv:.6f}")
+    assert fi >= 0.999 and fv >= 0.999
+
+
+@pytest.mark.parametrize("h,w,b", [(24, 32, 1), (37, 53, 2), (8, 33, 1), (3, 3, 1), (2, 2, 1), (384, 512, 1)])
+def test_ray_image_vs_oracle(front, oracle, h, w, b):
+    """Partial tiles, one-tile and minimum-size images (reflect padding needs >= 2)."""
+    g = torch.Generator().manual_seed(h * 1000 + w)
+    X11 = torch.randn(b, h, w, 3, generator=g) * torch.tensor([1.0, 1.0, 0.3]) + torch.tensor([0.0, 0.0, 2.0])
+    X11[0, 0, 0] = 0.0  # zero vector: F.normalize's eps clamp, result 0
+    ref, _, _ = oracle.prep_for_iter_proj(X11, X11, None)
+    rays = front.ray_image_with_grad(X11.cuda())
+    assert rays.shape == (b, h, w, 9)
+    assert torch.isfinite(rays).all()
+    assert (rays.cpu() - ref).abs().max().item() <= RAY_TOL
+    assert torch.equal(rays[0, 0, 0, :3].cpu(), torch.zeros(3))
+
+
+@pytest.mark.parametrize("h,w,b,seed,init", [(48, 64, 1, 0, "identity"), (96, 160, 3, 2, "true"),
+                                              (61, 83, 2, 3, "shifted"), (224, 224, 1, 4, "identity"),
+                                              (384, 512, 1, 5, "true")])
+def test_match_vs_oracle(front, oracle, h, w, b, seed, init):
+    m, idx_init = _case(h, w, b, seed, init)
+    idx, valid = front.match(m["X11"], m["X21"], m["D11"], m["D21"], idx_init)
+    io, vo = oracle.match(m["X11"], m["X21"], m["D11"], m["D21"], idx_init, **M)
+    fi = (idx.cpu() == io).float().mean().item()
+    fv = (valid.cpu() == vo).float().mean().item()
+    print(f"match {h}x{w} b={b} init={init}: idx agreement {fi:.6f}, valid agreement {fv:.6f}, "
+          f"valid fraction {valid.float().mean().item():.3f}")
+    assert idx.shape == (b, h * w) and valid.shape == (b, h * w, 1)
+    assert fi >= 0.999 and fv >= 0.999
+    assert (idx >= 0).all() and (idx < h * w).all()
+
+
+def test_match_equals_unfused_calls(front, backends):
+    """The fused call and the reference-shaped sequence over the same kernels (ray image from
+    m3r_prep_rays, then iter_proj, the torch epilogue of matching.py:66-85, refine_matches)
+    agree; differences can only come from F.normalize vs the in-kernel normalisation of X21."""
+    h, w, b = 120, 168, 2
+    m, idx_init = _case(h, w, b, 9, "true")
+    idx, valid = front.match(m["X11"], m["X21"], m["D11"], m["D21"], idx_init)
+    rays, pts, p0 = front.prep_for_iter_proj(m["X11"], m["X21"], idx_init)
+    p, conv = backends.iter_proj(rays, pts.contiguous(), p0.contiguous(), M["max_iter"], M["lambda_init"],
+                                 M["convergence_thresh"])
+    p1 = p.long()
+    bi = torch.arange(b, device="cuda")[:, None].repeat(1, h * w)
+    d = torch.linalg.norm(m["X11"][bi, p1[..., 1], p1[..., 0], :].reshape(b, h, w, 3) - m["X21"], dim=-1)
+    v2 = conv & (d < M["dist_thresh"]).view(b, -1)
+    (p1n,) = backends.refine_matches(m["D11"].half().contiguous(),
+                                     m["D21"].view(b, h * w, -1).half().contiguous(), p1,
+                                     M["radius"], M["dilation_max"])
+    idx2 = front.pixel_to_lin(p1n, w)
+    assert (idx == idx2).float().mean() >= 0.9995
+    assert (valid[..., 0] == v2).float().mean() >= 0.9995
+
+
+def test_match_radius0_and_generic_refine(front, oracle):
+    """radius == 0 skips refinement (matching.py:78); fdim != 24 takes the generic kernels."""
+    h, w, b = 40, 56, 1
+    m, idx_init = _case(h, w, b, 12, "true")
+    try:
+        front.set_config({"matching": dict(M, radius=0)})
+        idx, valid = front.match(m["X11"], m["X21"], None, None, idx_init)
+        io, vo = oracle.match(m["X11"], m["X21"], m["D11"], m["D21"], idx_init, **dict(M, radius=0))
+        assert (idx.cpu() == io).float().mean() >= 0.999 and (valid.cpu() == vo).float().mean() >= 0.999
+        front.set_config({"matching": dict(M, radius=2, dilation_max=3)})
+        m16 = synth.make_match_inputs(h, w, b=b, seed=12, fdim=16, device="cuda")
+        idx, valid = front.match(m16["X11"], m16["X21"], m16["D11"], m16["D21"], idx_init)
+        io, vo = oracle.match(m16["X11"], m16["X21"], m16["D11"], m16["D21"], idx_init,
+                              **dict(M, radius=2, dilation_max=3))
+        assert (idx.cpu() == io).float().mean() >= 0.999 and (valid.cpu() == vo).float().mean() >= 0.999
+    finally:
+        front.set_config({"matching": dict(M)})
+
+
+def test_match_errors_and_empty(front):
+    X = torch.rand(1, 16, 16, 3, device="cuda") + 1.0
+    D = torch.rand(1, 16, 16, 24, device="cuda")
+    with pytest.raises(RuntimeError):
+        front.match(X.cpu(), X, D, D)
+    with pytest.raises(RuntimeError):
+        front.match(X.double(), X.double(), D, D)
+    with pytest.raises(RuntimeError):
+        front.match(X, X, D, D, torch.zeros(1, 256, dtype=torch.int32, device="cuda"))
+    with pytest.raises(RuntimeError):
+        front.match(X, X[:, :8], D, D)
+    idx, valid = front.match(X[:0], X[:0], D[:0], D[:0])
+    assert idx.shape == (0, 256) and valid.shape == (0, 256, 1)
+    # identical views of a smooth surface: every interior pixel matches itself and is valid
+    m = synth.make_match_inputs(32, 48, b=1, seed=3, device="cuda")
+    idx, valid = front.match(m["X11"], m["X11"].clone(), m["D11"], m["D11"].clone())
+    own = torch.arange(32 * 48, device="cuda").view(32, 48)
+    assert valid.view(32, 48)[2:-2, 2:-2].all()
+    assert torch.equal(idx.view(32, 48)[2:-2, 2:-2], own[2:-2, 2:-2])

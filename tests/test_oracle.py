@@ -247,3 +247,27 @@ def test_golden_gn(oracle, path):
         assert (T - rT).abs().max() <= 1e-4 * max(1.0, rT.abs().max().item()), (kind, key)
         if iters == 1:
             assert (dx - rdx).norm() <= 1e-4 * rdx.norm() + 1e-7, (kind, (dx - rdx).norm() / rdx.norm())
+
+
+@pytest.mark.parametrize("path", _golden("front_") or [None])
+def test_golden_front_end(oracle, path):
+    """Oracle restatement of the Python glue around the kernels (oracle.match,
+    oracle.prep_for_iter_proj) vs the reference's own matching.py / image.py run on the same
+    inputs (tests/golden/make_golden_front.py)."""
+    if path is None:
+        pytest.skip("no golden front-end vectors committed yet")
+    z = np.load(path)
+    X11, X21 = torch.from_numpy(z["X11"]), torch.from_numpy(z["X21"])
+    D11 = torch.from_numpy(z["D11_f16"]).view(torch.float16)
+    D21 = torch.from_numpy(z["D21_f16"]).view(torch.float16)
+    idx_init = torch.from_numpy(z["idx_init"]) if "idx_init" in z else None
+    rays, pts, p_init = oracle.prep_for_iter_proj(X11, X21, idx_init)
+    assert torch.equal(rays, torch.from_numpy(z["ref_rays"]))
+    assert torch.equal(pts, torch.from_numpy(z["ref_pts"]))
+    assert torch.equal(p_init, torch.from_numpy(z["ref_p_init"]))
+    cfg = {k: z[k].item() for k in ("max_iter", "lambda_init", "convergence_thresh", "dist_thresh",
+                                    "radius", "dilation_max")}
+    idx, valid = oracle.match(X11, X21, D11, D21, idx_init, **cfg)
+    assert idx.dtype == torch.int64 and valid.dtype == torch.bool and valid.shape == (*idx.shape, 1)
+    assert torch.equal(idx, torch.from_numpy(z["ref_idx"]))
+    assert torch.equal(valid, torch.from_numpy(z["ref_valid"]))
