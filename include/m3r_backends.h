@@ -122,6 +122,58 @@ int m3r_match(const float *X11, const float *X21, const void *D11, const void *D
               int dilation_max, void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Tracking pose solve -- replaces the bodies of
+ * `FrameTracker.opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid)` and
+ * `FrameTracker.opt_pose_calib_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K,
+ * img_size)` (mast3r_slam/tracker.py:173-215, 217-266) including `solve` (:157-171), the
+ * geometry helpers they call (geometry.py:12-33, 45-53, 64-107), `check_convergence` and
+ * `huber` (nonlinear_optimizer.py:5-35) and the lietorch Sim3 algebra around them: one
+ * cooperative kernel runs all iterations on the device, no host synchronisation.
+ *   Xf          [n_f,3] f32   frame pointmap.  With idx_f2k == NULL it is the already gathered
+ *                             `Xf[idx_f2k]` of tracker.py:155 (n_f == n); otherwise the
+ *                             canonical pointmap, gathered inside the kernel
+ *   idx_f2k     [n] i64|NULL  for keyframe point k, its match in the frame
+ *   Xk          [n,3]  f32    keyframe pointmap (rays only; may be NULL for calib)
+ *   Qk          [n]    f32    match confidence sqrt(Qff[idx] * Qkf) (tracker.py:41)
+ *   valid       [n]    u8     valid_opt (tracker.py:62-66)
+ *   meas_k      [n,3]  f32    calib only: (u, v, log z) of the keyframe points (:145-150)
+ *   valid_meas_k[n]    u8     calib only
+ *   T_WCf,T_WCk [8]    f32    lietorch.Sim3.data rows (t xyz, q xyzw, s), 16-byte aligned
+ *   result      device struct, see below; status CHOLESKY_FAILED is where the reference's
+ *               torch.linalg.cholesky raises (tracker.py:168, caught at :90-92)
+ *   scratch     m3r_track_scratch_doubles() doubles of caller-owned device memory
+ * ------------------------------------------------------------------------------------- */
+#define M3R_TRACK_OK 0
+#define M3R_TRACK_CHOLESKY_FAILED 1
+
+typedef struct m3r_track_params {
+  int kind;                /* M3R_GN_RAYS (ray + distance) or M3R_GN_CALIB (pixel + log depth) */
+  int max_iters;           /* config tracking.max_iters */
+  float rel_error;         /* tracking.rel_error  */
+  float delta_norm;        /* tracking.delta_norm */
+  float huber_k;           /* tracking.huber      */
+  float sigma_a, sigma_b;  /* rays: sigma_ray, sigma_dist; calib: sigma_pixel, sigma_depth */
+  float K[9];              /* calib: intrinsics, row-major */
+  int height, width;       /* calib: img_size */
+  float pixel_border;      /* calib: tracking.pixel_border */
+  float z_eps;             /* calib: tracking.depth_eps */
+} m3r_track_params;
+
+typedef struct m3r_track_result {
+  float T_WCf[8];      /* T_WCk * T_CkCf (tracker.py:213) */
+  float T_CkCf[8];     /* the optimised relative pose */
+  int32_t status;      /* M3R_TRACK_* */
+  int32_t iterations;  /* executed iterations */
+  double cost;         /* 0.5 * b^T b of the last linearisation (tracker.py:166) */
+} m3r_track_result;
+
+int64_t m3r_track_scratch_doubles(void);
+int m3r_track_pose(const m3r_track_params *params, const float *Xf, int64_t n_f,
+                   const int64_t *idx_f2k, const float *Xk, const float *Qk, const uint8_t *valid,
+                   const float *meas_k, const uint8_t *valid_meas_k, int64_t n, const float *T_WCf,
+                   const float *T_WCk, m3r_track_result *result, double *scratch, void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * Gauss-Newton on the Sim(3) keyframe graph.
  *
  * A workspace caches device scratch (per-edge blocks, the assembled system, index maps)

@@ -59,6 +59,40 @@ class GnProblem(ctypes.Structure):
     ]
 
 
+class TrackParams(ctypes.Structure):
+    """Mirror of `m3r_track_params` (include/m3r_backends.h)."""
+
+    _fields_ = [
+        ("kind", c_int),
+        ("max_iters", c_int),
+        ("rel_error", c_float),
+        ("delta_norm", c_float),
+        ("huber_k", c_float),
+        ("sigma_a", c_float),
+        ("sigma_b", c_float),
+        ("K", c_float * 9),
+        ("height", c_int),
+        ("width", c_int),
+        ("pixel_border", c_float),
+        ("z_eps", c_float),
+    ]
+
+
+class TrackResult(ctypes.Structure):
+    """Mirror of `m3r_track_result` (include/m3r_backends.h); lives in device memory."""
+
+    _fields_ = [
+        ("T_WCf", c_float * 8),
+        ("T_CkCf", c_float * 8),
+        ("status", ctypes.c_int32),
+        ("iterations", ctypes.c_int32),
+        ("cost", ctypes.c_double),
+    ]
+
+
+TRACK_OK, TRACK_CHOLESKY_FAILED = 0, 1
+
+
 def _sig(name, restype, argtypes):
     fn = getattr(lib, name)
     fn.restype = restype
@@ -91,6 +125,12 @@ match = _sig(
     "m3r_match",
     c_int,
     [c_void_p] * 4 + [c_int] * 2 + [c_void_p] * 5 + [c_int] * 4 + [c_float] * 3 + [c_int] * 2 + [c_void_p],
+)
+track_scratch_doubles = _sig("m3r_track_scratch_doubles", c_int64, [])
+track_pose = _sig(
+    "m3r_track_pose",
+    c_int,
+    [ctypes.POINTER(TrackParams), c_void_p, c_int64] + [c_void_p] * 6 + [c_int64] + [c_void_p] * 5,
 )
 
 gn_workspace_create = _sig("m3r_gn_workspace_create", c_int, [ctypes.POINTER(c_void_p)])
@@ -150,6 +190,8 @@ EXPORTS = [
     "m3r_refine_matches_v",
     "m3r_prep_rays",
     "m3r_match",
+    "m3r_track_scratch_doubles",
+    "m3r_track_pose",
     "m3r_gn_workspace_create",
     "m3r_gn_workspace_destroy",
     "m3r_gauss_newton_rays",

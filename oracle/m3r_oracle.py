@@ -231,3 +231,196 @@ def match(X11, X21, D11, D21, idx_1_to_2_init=None, *, max_iter=10, lambda_init=
                                dilation_max)
     idx_1_to_2 = p1[..., 0] + w * p1[..., 1]  # pixel_to_lin, matching.py:13-15
     return idx_1_to_2, valid_proj2.unsqueeze(-1)
+
+
+# --------------------------------------------------------------------------------------------
+# tracking pose solve: CPU restatement of FrameTracker.opt_pose_ray_dist_sim3
+# / opt_pose_calib_sim3 / solve (mast3r_slam/tracker.py:157-266), the geometry helpers they call
+# (mast3r_slam/geometry.py:12-33 point_to_ray_dist, :45-53 act_Sim3, :64-107 project_calib) and
+# nonlinear_optimizer.py:5-35 (check_convergence, huber).  Pinned by tests/golden/track_*.npz,
+# which tests/golden/make_golden_track.py writes by running the reference's own tracker.py /
+# geometry.py / nonlinear_optimizer.py on CPU with `lietorch` replaced by the Sim3 class below.
+# --------------------------------------------------------------------------------------------
+class Sim3:
+    """CPU stand-in for lietorch.Sim3: the reference's pip dependency `lietorch @ git+https://
+    github.com/princeton-vl/lietorch.git` (pyproject.toml:15, unpinned, not vendored, CUDA-only
+    build).  data [..., 8] = (t xyz, q xyzw, s).  Restates the published group operations of
+    lietorch/include/{sim3,rxso3,so3}.h: act p -> s R p + t; inv; composition; retr(a) =
+    Exp(a) * X (left), with Exp through this oracle's C restatement of the reference's own copy
+    of it (gn_kernels.cu:323-413, itself pinned by the Gauss-Newton golden vectors)."""
+
+    def __init__(self, data):
+        self.data = data
+
+    @staticmethod
+    def Identity(n, **kw):
+        d = torch.zeros((n, 8), dtype=torch.float32)
+        d[:, 6] = 1.0
+        d[:, 7] = 1.0
+        return Sim3(d)
+
+    @staticmethod
+    def _rot(q, p):
+        # Eigen::Quaternion::_transformVector: uv = 2 qv x p; p + w uv + qv x uv
+        qv, qw = q[..., :3], q[..., 3:4]
+        uv = 2.0 * torch.linalg.cross(qv.expand_as(p), p)
+        return p + qw * uv + torch.linalg.cross(qv.expand_as(p), uv)
+
+    @staticmethod
+    def _qmul(a, b):
+        ax, ay, az, aw = a.unbind(-1)
+        bx, by, bz, bw = b.unbind(-1)
+        return torch.stack((aw * bx + ax * bw + ay * bz - az * by,
+                            aw * by - ax * bz + ay * bw + az * bx,
+                            aw * bz + ax * by - ay * bx + az * bw,
+                            aw * bw - ax * bx - ay * by - az * bz), dim=-1)
+
+    def act(self, p):
+        t, q, s = self.data[..., :3], self.data[..., 3:7], self.data[..., 7:8]
+        return s * Sim3._rot(q, p) + t
+
+    def inv(self):
+        t, q, s = self.data[..., :3], self.data[..., 3:7], self.data[..., 7:8]
+        qi = q * torch.tensor([-1.0, -1.0, -1.0, 1.0])
+        si = 1.0 / s
+        return Sim3(torch.cat((-(si * Sim3._rot(qi, t)), qi, si), dim=-1))
+
+    def __mul__(self, other):
+        t, q, s = self.data[..., :3], self.data[..., 3:7], self.data[..., 7:8]
+        t2, q2, s2 = other.data[..., :3], other.data[..., 3:7], other.data[..., 7:8]
+        return Sim3(torch.cat((s * Sim3._rot(q, t2) + t, Sim3._qmul(q, q2), s * s2), dim=-1))
+
+    def retr(self, a):
+        d = self.data.reshape(-1, 8).contiguous().clone()
+        return Sim3(pose_retr(d, a.reshape(-1, 7).contiguous(), num_fix=0).view(self.data.shape))
+
+
+TRACK_DEFAULTS = dict(max_iters=50, C_conf=0.0, Q_conf=1.5, rel_error=1e-3, delta_norm=1e-3,
+                      huber=1.345, sigma_ray=0.003, sigma_dist=10.0, sigma_pixel=1.0,
+                      sigma_depth=10.0, pixel_border=-10, depth_eps=1e-6, min_match_frac=0.05,
+                      match_frac_thresh=0.333)  # config/base.yaml:16-31
+
+
+def _huber(r, k):  # nonlinear_optimizer.py:29-35
+    r_abs = torch.abs(r)
+    return torch.where(r_abs < k, torch.ones(1, dtype=r.dtype), k / r_abs)
+
+
+def _track_solve(sqrt_info, r, J, k):  # tracker.py:157-171
+    whitened_r = sqrt_info * r
+    robust_sqrt_info = sqrt_info * torch.sqrt(_huber(whitened_r, k))
+    mdim = J.shape[-1]
+    A = (robust_sqrt_info[..., None] * J).view(-1, mdim)
+    b = (robust_sqrt_info * r).view(-1, 1)
+    H = A.T @ A
+    g = -A.T @ b
+    cost = 0.5 * (b.T @ b).item()
+    L = torch.linalg.cholesky(H, upper=False)  # raises when H is not positive definite
+    tau = torch.cholesky_solve(g, L, upper=False).view(1, -1)
+    return tau, cost, H, g
+
+
+def _converged(rel_error, delta_norm, old_cost, new_cost, delta):  # nonlinear_optimizer.py:5-26
+    import math
+
+    rel_dec = math.fabs((old_cost - new_cost) / old_cost) if old_cost != 0 else float("nan")
+    return rel_dec < rel_error or float(torch.linalg.norm(delta)) < delta_norm
+
+
+def _ray_dist(X):  # geometry.py:12-33
+    d = torch.linalg.norm(X, dim=-1, keepdim=True)
+    d_inv = 1.0 / d
+    r = d_inv * X
+    rd = torch.cat((r, d), dim=-1)
+    eye = torch.eye(3, dtype=X.dtype).expand(*X.shape[:-1], 3, 3)
+    dr_dX = d_inv.unsqueeze(-1) * (eye - (d_inv ** 2).unsqueeze(-1) * (X.unsqueeze(-1) @ X.unsqueeze(-2)))
+    return rd, torch.cat((dr_dX, r.unsqueeze(-2)), dim=-2)
+
+
+def _act_jac(T, p):  # geometry.py:45-53
+    pW = T.act(p)
+    x, y, z = pW.unbind(-1)
+    o = torch.zeros_like(x)
+    skew = torch.stack([o, -z, y, z, o, -x, -y, x, o], dim=-1).view(*pW.shape[:-1], 3, 3)
+    eye = torch.eye(3, dtype=pW.dtype).expand(*pW.shape[:-1], 3, 3)
+    return pW, torch.cat([eye, -skew, pW.unsqueeze(-1)], dim=-1)
+
+
+def track_pose_rays(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=None, trace=None):
+    """tracker.py:173-215.  Xf [n,3] (already gathered by idx_f2k), Xk [n,3], poses [1,8],
+    Qk [n,1], valid [n,1] bool.  Returns (T_WCf [1,8], T_CkCf [1,8], iterations, last cost)."""
+    c = dict(TRACK_DEFAULTS, **(cfg or {}))
+    Xf, Xk, Qk = _cpu(Xf, torch.float32), _cpu(Xk, torch.float32), _cpu(Qk, torch.float32)
+    valid = _cpu(valid).bool()
+    Twf, Twk = Sim3(_cpu(T_WCf, torch.float32)), Sim3(_cpu(T_WCk, torch.float32))
+    si_ray = 1 / c["sigma_ray"] * valid * torch.sqrt(Qk)
+    si_dist = 1 / c["sigma_dist"] * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((si_ray.repeat(1, 3), si_dist), dim=1)
+    T = Twk.inv() * Twf
+    d = torch.linalg.norm(Xk, dim=-1, keepdim=True)
+    rd_k = torch.cat((Xk / d, d), dim=-1)
+    old_cost, cost, it = float("inf"), 0.0, 0
+    for step in range(c["max_iters"]):
+        P, dP = _act_jac(T, Xf)
+        rd_f, drd = _ray_dist(P)
+        r = rd_k - rd_f
+        J = -drd @ dP
+        tau, cost, H, g = _track_solve(sqrt_info, r, J, c["huber"])
+        if trace is not None:
+            trace.append(dict(H=H, g=g, cost=cost, tau=tau, T=T.data.clone()))
+        T = T.retr(tau)
+        it = step + 1
+        if _converged(c["rel_error"], c["delta_norm"], old_cost, cost, tau):
+            break
+        old_cost = cost
+    return (Twk * T).data, T.data, it, cost
+
+
+def track_pose_calib(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size, cfg=None,
+                     trace=None):
+    """tracker.py:217-266 with geometry.project_calib (geometry.py:64-107).  meas_k [n,3] =
+    (u, v, log z) of the keyframe points, valid_meas_k [n,1]; K [3,3]; img_size (h, w)."""
+    c = dict(TRACK_DEFAULTS, **(cfg or {}))
+    Xf, Xk, Qk = _cpu(Xf, torch.float32), _cpu(Xk, torch.float32), _cpu(Qk, torch.float32)
+    meas_k, K = _cpu(meas_k, torch.float32), _cpu(K, torch.float32)
+    valid, valid_meas_k = _cpu(valid).bool(), _cpu(valid_meas_k).bool()
+    Twf, Twk = Sim3(_cpu(T_WCf, torch.float32)), Sim3(_cpu(T_WCk, torch.float32))
+    si_pix = 1 / c["sigma_pixel"] * valid * torch.sqrt(Qk)
+    si_dep = 1 / c["sigma_depth"] * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((si_pix.repeat(1, 2), si_dep), dim=1)
+    T = Twk.inv() * Twf
+    fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+    border, z_eps = c["pixel_border"], c["depth_eps"]
+    old_cost, cost, it = float("inf"), 0.0, 0
+    for step in range(c["max_iters"]):
+        P, dP = _act_jac(T, Xf)
+        p = (K @ P[..., None]).squeeze(-1)
+        p = (p / p[..., 2:3])[..., :2]
+        u, v = p[..., 0:1], p[..., 1:2]
+        x, y, z = P[..., 0:1], P[..., 1:2], P[..., 2:3]
+        valid_z = z > z_eps
+        valid_proj = ((u > border) & (u < img_size[1] - 1 - border) & (v > border) &
+                      (v < img_size[0] - 1 - border) & valid_z)
+        logz = torch.log(z)
+        logz[~valid_z] = 0.0
+        pz = torch.cat((p, logz), dim=-1)
+        z_inv = 1.0 / z[..., 0]
+        dpz = torch.zeros(*P.shape[:-1], 3, 3)
+        dpz[..., 0, 0] = fx
+        dpz[..., 1, 1] = fy
+        dpz[..., 0, 2] = -fx * x[..., 0] * z_inv
+        dpz[..., 1, 2] = -fy * y[..., 0] * z_inv
+        dpz *= z_inv[..., None, None]
+        dpz[..., 2, 2] = z_inv
+        sqrt_info2 = (valid_proj & valid_meas_k) * sqrt_info
+        r = meas_k - pz
+        J = -dpz @ dP
+        tau, cost, H, g = _track_solve(sqrt_info2, r, J, c["huber"])
+        if trace is not None:
+            trace.append(dict(H=H, g=g, cost=cost, tau=tau, T=T.data.clone()))
+        T = T.retr(tau)
+        it = step + 1
+        if _converged(c["rel_error"], c["delta_norm"], old_cost, cost, tau):
+            break
+        old_cost = cost
+    return (Twk * T).data, T.data, it, cost

@@ -267,3 +267,44 @@ GN_DEFAULTS = dict(sigma_ray=0.003, sigma_dist=10.0, sigma_pixel=1.0, sigma_dept
                    max_iter=10, delta_thresh=1e-8)
 MATCH_DEFAULTS = dict(max_iter=10, lambda_init=1e-8, convergence_thresh=1e-6, dist_thresh=0.1,
                       radius=3, dilation_max=5)
+
+
+# parameters from config/base.yaml:16-31 (tracking)
+TRACK_DEFAULTS = dict(max_iters=50, C_conf=0.0, Q_conf=1.5, rel_error=1e-3, delta_norm=1e-3,
+                      huber=1.345, sigma_ray=0.003, sigma_dist=10.0, sigma_pixel=1.0,
+                      sigma_depth=10.0, pixel_border=-10, depth_eps=1e-6, min_match_frac=0.05,
+                      match_frac_thresh=0.333)
+
+
+def make_track_inputs(h, w, seed=0, device="cpu", pose_noise=0.03, point_noise=2e-3):
+    """BASELINE config 2's pose solve: one frame f against the last keyframe k, as
+    FrameTracker.track hands it to opt_pose_* (tracker.py:29-90, 129-155).
+
+    Returns dict: Xf_canon/Xk [n,3], Cf/Ck [n,1], idx_f2k [n] (for keyframe point k, its match in
+    the frame), valid_match_k [n,1] bool, Qff/Qkf [n,1] (match confidences of the two views),
+    T_WCf_init/T_WCf_true/T_WCk [1,8], K [3,3], and the derived arguments of the pose solve:
+    Xf [n,3] = Xf_canon[idx_f2k], Qk, valid_opt, meas_k [n,3], valid_meas_k [n,1]."""
+    g = make_graph(2, h, w, seed=seed, device=device, pose_noise=pose_noise, point_noise=point_noise)
+    n = h * w
+    e = int(((g["ii"] == 1) & (g["jj"] == 0)).nonzero()[0, 0])
+    idx = g["idx_ii2jj"][e].contiguous()
+    valid_match = g["valid_match"][e].contiguous()
+    gen = torch.Generator().manual_seed(7000 + seed)
+    Qff = torch.exp(1.0 + 0.5 * torch.randn(n, 1, generator=gen)).to(device)
+    Qkf = torch.exp(1.0 + 0.5 * torch.randn(n, 1, generator=gen)).to(device)
+    Xf_canon, Xk = g["Xs"][1].contiguous(), g["Xs"][0].contiguous()
+    Cf_canon, Ck = g["Cs"][1].contiguous(), g["Cs"][0].contiguous()
+    Qk = torch.sqrt(Qff[idx] * Qkf)  # tracker.py:41
+    Cf = Cf_canon[idx]
+    T = TRACK_DEFAULTS
+    valid_opt = valid_match & (Cf > T["C_conf"]) & (Ck > T["C_conf"]) & (Qk > T["Q_conf"])  # :62-66
+    vv, uu = torch.meshgrid(torch.arange(h, device=device), torch.arange(w, device=device), indexing="ij")
+    uv = torch.stack((uu, vv), dim=-1).view(-1, 2).float()
+    valid_meas = Xk[..., 2:3] > T["depth_eps"]
+    meas = torch.cat((uv, torch.log(Xk[..., 2:3].clamp_min(1e-30))), dim=-1)
+    meas[~valid_meas.repeat(1, 3)] = 0.0
+    return dict(Xf_canon=Xf_canon, Xk=Xk, Cf_canon=Cf_canon, Ck=Ck, idx_f2k=idx, valid_match_k=valid_match,
+                Qff=Qff, Qkf=Qkf, T_WCk=g["Twc_init"][0:1].contiguous(),
+                T_WCf_init=g["Twc_init"][1:2].contiguous(), T_WCf_true=g["Twc_true"][1:2].contiguous(),
+                K=g["K"], h=h, w=w, n=n, Xf=Xf_canon[idx].contiguous(), Qk=Qk.contiguous(), Cf=Cf.contiguous(),
+                valid_opt=valid_opt.contiguous(), meas_k=meas.contiguous(), valid_meas_k=valid_meas.contiguous())

@@ -271,3 +271,53 @@ def test_golden_front_end(oracle, path):
     assert idx.dtype == torch.int64 and valid.dtype == torch.bool and valid.shape == (*idx.shape, 1)
     assert torch.equal(idx, torch.from_numpy(z["ref_idx"]))
     assert torch.equal(valid, torch.from_numpy(z["ref_valid"]))
+
+
+TRACK_KEYS = ("max_iters", "rel_error", "delta_norm", "huber", "sigma_ray", "sigma_dist", "sigma_pixel",
+              "sigma_depth", "pixel_border", "depth_eps")
+
+
+def load_track_golden(path):
+    z = np.load(path)
+    t = {k: torch.from_numpy(z[k]) for k in ("Xf", "Xk", "Qk", "valid_opt", "meas_k", "valid_meas_k", "K",
+                                             "T_WCk", "T_WCf_init", "T_WCf_true")}
+    cfg = {k: z[k].item() for k in TRACK_KEYS}
+    ref = {k: torch.from_numpy(z[k]) for k in z.files if k.startswith("ref_")}
+    return t, cfg, ref, (int(z["h"]), int(z["w"]))
+
+
+@pytest.mark.parametrize("path", _golden("track_") or [None])
+def test_golden_tracking(oracle, path):
+    """oracle.track_pose_rays / track_pose_calib vs the reference's own tracker.py loop run on
+    the same inputs (tests/golden/make_golden_track.py)."""
+    if path is None:
+        pytest.skip("no golden tracking vectors committed yet")
+    t, cfg, ref, img = load_track_golden(path)
+    Twf, Tkf, it, cost = oracle.track_pose_rays(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"],
+                                                t["valid_opt"], cfg)
+    assert (Twf - ref["ref_rays_T_WCf"]).abs().max() < 1e-5
+    assert (Tkf - ref["ref_rays_T_CkCf"]).abs().max() < 1e-5
+    Twf, Tkf, it, cost = oracle.track_pose_calib(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"],
+                                                 t["valid_opt"], t["meas_k"], t["valid_meas_k"], t["K"],
+                                                 img, cfg)
+    assert (Twf - ref["ref_calib_T_WCf"]).abs().max() < 1e-5
+    assert (Tkf - ref["ref_calib_T_CkCf"]).abs().max() < 1e-5
+
+
+def test_sim3_stand_in_group_laws(oracle):
+    S = oracle.Sim3
+    g = torch.Generator().manual_seed(0)
+    d = torch.randn(4, 8, generator=g)
+    d[:, 3:7] /= d[:, 3:7].norm(dim=-1, keepdim=True)
+    d[:, 7] = torch.exp(0.3 * d[:, 7])
+    A, B = S(d[:2]), S(d[2:])
+    p = torch.randn(2, 3, generator=g)
+    assert ((A * B).act(p) - A.act(B.act(p))).abs().max() < 1e-5
+    assert (A.inv().act(A.act(p)) - p).abs().max() < 1e-5
+    I = (A.inv() * A).data
+    assert (I - S.Identity(2).data).abs().max() < 1e-6
+    # retr(0) is the identity; retr is a LEFT update: a pure translation tau adds to t
+    assert torch.equal(A.retr(torch.zeros(2, 7)).data, A.data)
+    tau = torch.zeros(2, 7)
+    tau[:, :3] = torch.tensor([0.1, -0.2, 0.3])
+    assert (A.retr(tau).data[:, :3] - (A.data[:, :3] + tau[:, :3])).abs().max() < 1e-6
