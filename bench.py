@@ -263,6 +263,66 @@ def time_matching_e2e(be, sets, M, steps, warmup, world):
     return ms, h2d, d2h
 
 
+def time_tracking(steps, warmup, cpu=True):
+    """The per-frame pose solve of BASELINE config 2 (tracker.py:173-266) at
+    512x384: one cooperative launch per call.  `us_per_iter` comes from a fixed-iteration run
+    (stop tests off) so launch + staging and the per-iteration cost separate."""
+    import synth
+    from mast3r_slam_backends import tracking as tr
+
+    t = synth.make_track_inputs(H, W, seed=3, device="cuda", pose_noise=0.03)
+    out = {}
+
+    def run(kind, cfg, reps):
+        tr.set_config({"tracking": cfg})
+        if kind == "rays":
+            fn = lambda: tr.opt_pose_ray_dist_sim3(t["Xf_canon"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"],
+                                                   t["valid_opt"], idx_f2k=t["idx_f2k"], check=False)
+        else:
+            fn = lambda: tr.opt_pose_calib_sim3(t["Xf_canon"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"],
+                                                t["valid_opt"], t["meas_k"], t["valid_meas_k"], t["K"], (H, W),
+                                                idx_f2k=t["idx_f2k"], check=False)
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(reps):
+            fn()
+        t1.record()
+        torch.cuda.synchronize()
+        return t0.elapsed_time(t1) / reps
+
+    base = dict(synth.TRACK_DEFAULTS)
+    for kind in ("rays", "calib"):
+        ms = run(kind, base, steps)
+        # iteration count of the default configuration (one checked call)
+        tr.set_config({"tracking": base})
+        if kind == "rays":
+            tr.opt_pose_ray_dist_sim3(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"], t["valid_opt"])
+        else:
+            tr.opt_pose_calib_sim3(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"], t["valid_opt"],
+                                   t["meas_k"], t["valid_meas_k"], t["K"], (H, W))
+        iters = tr.last_info.iterations
+        fixed = dict(base, rel_error=0.0, delta_norm=0.0)
+        ms5 = run(kind, dict(fixed, max_iters=5), steps)
+        ms45 = run(kind, dict(fixed, max_iters=45), steps)
+        out[kind] = {"ms_per_call": ms, "iterations": iters, "us_per_iter": (ms45 - ms5) / 40 * 1e3,
+                     "fixed_us": (ms5 - 5 * (ms45 - ms5) / 40) * 1e3, "gpu_launches_per_call": 1}
+    tr.set_config({"tracking": base})
+    if cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import m3r_oracle as oracle
+
+        c = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in t.items()}
+        t0 = time.perf_counter()
+        _, _, it, _ = oracle.track_pose_rays(c["Xf"], c["Xk"], c["T_WCf_init"], c["T_WCk"], c["Qk"], c["valid_opt"])
+        out["cpu_port_rays_ms_per_call"] = (time.perf_counter() - t0) * 1e3
+        out["cpu_port_iterations"] = it
+        out["cpu_port_threads"] = torch.get_num_threads()
+    return out
+
+
 # --------------------------------------------------------------------------------------------
 # Gauss-Newton (64-keyframe graph; edges sharded over the ranks at N > 1)
 # --------------------------------------------------------------------------------------------
@@ -542,6 +602,7 @@ def main():
 
     if rank == 0 and not args.profile:
         line["front_end"] = time_front_end(be, sets, M, max(args.steps // 4, 10), 3)
+        line["tracking"] = time_tracking(max(args.steps // 4, 10), 3)
 
     # ---- Gauss-Newton
     g = None

@@ -138,10 +138,13 @@ int m3r_match(const float *X11, const float *X21, const void *D11, const void *D
  *   valid       [n]    u8     valid_opt (tracker.py:62-66)
  *   meas_k      [n,3]  f32    calib only: (u, v, log z) of the keyframe points (:145-150)
  *   valid_meas_k[n]    u8     calib only
+ *   K           [3,3]  f32    calib only: intrinsics, row-major, on the device
  *   T_WCf,T_WCk [8]    f32    lietorch.Sim3.data rows (t xyz, q xyzw, s), 16-byte aligned
  *   result      device struct, see below; status CHOLESKY_FAILED is where the reference's
  *               torch.linalg.cholesky raises (tracker.py:168, caught at :90-92)
- *   scratch     m3r_track_scratch_doubles() doubles of caller-owned device memory
+ *   scratch     m3r_track_scratch_doubles() doubles of caller-owned device memory, ZEROED once
+ *               when allocated and then passed to every call (it carries the grid-barrier
+ *               counter from launch to launch); one scratch per stream
  * ------------------------------------------------------------------------------------- */
 #define M3R_TRACK_OK 0
 #define M3R_TRACK_CHOLESKY_FAILED 1
@@ -153,7 +156,6 @@ typedef struct m3r_track_params {
   float delta_norm;        /* tracking.delta_norm */
   float huber_k;           /* tracking.huber      */
   float sigma_a, sigma_b;  /* rays: sigma_ray, sigma_dist; calib: sigma_pixel, sigma_depth */
-  float K[9];              /* calib: intrinsics, row-major */
   int height, width;       /* calib: img_size */
   float pixel_border;      /* calib: tracking.pixel_border */
   float z_eps;             /* calib: tracking.depth_eps */
@@ -170,8 +172,9 @@ typedef struct m3r_track_result {
 int64_t m3r_track_scratch_doubles(void);
 int m3r_track_pose(const m3r_track_params *params, const float *Xf, int64_t n_f,
                    const int64_t *idx_f2k, const float *Xk, const float *Qk, const uint8_t *valid,
-                   const float *meas_k, const uint8_t *valid_meas_k, int64_t n, const float *T_WCf,
-                   const float *T_WCk, m3r_track_result *result, double *scratch, void *stream);
+                   const float *meas_k, const uint8_t *valid_meas_k, const float *K, int64_t n,
+                   const float *T_WCf, const float *T_WCk, m3r_track_result *result, double *scratch,
+                   void *stream);
 
 /* ---------------------------------------------------------------------------------------
  * Gauss-Newton on the Sim(3) keyframe graph.

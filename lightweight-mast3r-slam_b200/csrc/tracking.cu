@@ -20,11 +20,7 @@
 //    one small device struct.
 #include "m3r_common.cuh"
 
-#include <cooperative_groups.h>
-
 #include "sim3.cuh"
-
-namespace cg = cooperative_groups;
 
 namespace m3r {
 
@@ -32,7 +28,6 @@ constexpr int kTrThreads = 512;
 constexpr int kTrWarps = kTrThreads / 32;
 constexpr int kTrAcc = 36;        // 28 (upper triangle of H) + 7 (J^T W r) + 1 (cost)
 constexpr int kTrCap = 6144;      // staged points per CTA (8 floats each = 192 KB)
-constexpr int kTrMaxGrid = 2 * kNumSMs;
 
 struct TrackArgs {
   const float *Xf;            // [n_f,3] frame pointmap (gathered through idx when non-null)
@@ -45,53 +40,101 @@ struct TrackArgs {
   const float *T_WCf, *T_WCk; // [8]
   m3r_track_result *result;
   double *partial;            // [2][grid][kTrAcc]
+  unsigned *barrier;          // [0] arrival counter (monotonic), [1] its value at kernel start
+  const float *Kp;            // [9] calib intrinsics (device)
   int n;
   int n_f;                    // rows of Xf (bounds the gather)
   int max_iters;
   float inv_sigma_a, inv_sigma_b, huber_k, rel_error, delta_norm;
-  float K[9];
   float u_lo, u_hi, v_lo, v_hi, z_eps;
 };
 
 struct TrackSmem {
   double warp_part[kTrWarps][kTrAcc];
+  double all_part[kNumSMs * kTrAcc];
   double sys[kTrAcc];
   Pose T;
   int stop;    // 0 continue, 1 converged, 2 factorisation failed
   double cost;
 };
 
-// 7x7 SPD solve H x = g in fp64 (H given by its upper triangle, row-major packed).
-// Returns false when a pivot is not positive (torch.linalg.cholesky would raise).
-__device__ bool solve7(const double *__restrict__ sys, double x[7]) {
-  double L[7][7];
-  int k = 0;
-  for (int i = 0; i < 7; i++)
-    for (int j = i; j < 7; j++) L[j][i] = sys[k++];  // lower triangle
+// 7x7 SPD solve H x = g in fp64 (H given by its upper triangle, row-major packed).  Fully
+// unrolled: the factor lives in registers, one rsqrt per pivot and no divisions.  Returns
+// false when a pivot is not positive (torch.linalg.cholesky would raise).
+__device__ __forceinline__ bool solve7(const double *__restrict__ sys, double x[7]) {
+  double L[7][7], ri[7];
+  {
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 7; i++)
+#pragma unroll
+      for (int j = i; j < 7; j++) L[j][i] = sys[k++];  // lower triangle
+  }
+  bool ok = true;
+#pragma unroll
   for (int j = 0; j < 7; j++) {
     double d = L[j][j];
+#pragma unroll
     for (int p = 0; p < j; p++) d -= L[j][p] * L[j][p];
-    if (!(d > 0.0) || !isfinite(d)) return false;
-    const double r = sqrt(d), ri = 1.0 / r;
-    L[j][j] = r;
+    ok = ok && (d > 0.0) && isfinite(d);
+    ri[j] = rsqrt(d);
+#pragma unroll
     for (int i = j + 1; i < 7; i++) {
       double v = L[i][j];
+#pragma unroll
       for (int p = 0; p < j; p++) v -= L[i][p] * L[j][p];
-      L[i][j] = v * ri;
+      L[i][j] = v * ri[j];
     }
   }
   double y[7];
+#pragma unroll
   for (int i = 0; i < 7; i++) {
     double v = sys[28 + i];
+#pragma unroll
     for (int p = 0; p < i; p++) v -= L[i][p] * y[p];
-    y[i] = v / L[i][i];
+    y[i] = v * ri[i];
   }
+#pragma unroll
   for (int i = 6; i >= 0; i--) {
     double v = y[i];
+#pragma unroll
     for (int p = i + 1; p < 7; p++) v -= L[p][i] * x[p];
-    x[i] = v / L[i][i];
+    x[i] = v * ri[i];
   }
-  return true;
+  return ok;
+}
+
+// Grid barrier on a monotonically increasing arrival counter (scratch word 0); `target` is
+// the value the counter reaches when every CTA has arrived.  One release add and an acquire
+// poll by thread 0: about half the cost of cooperative_groups' grid.sync(), whose L1
+// invalidate this kernel does not need (the partials are read with ld.global.cg).
+__device__ __forceinline__ void grid_barrier(unsigned *counter, unsigned target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    } while (static_cast<int>(v - target) < 0);
+  }
+  __syncthreads();
+}
+
+// Sum each of v[0..31] over the 32 lanes with 31 shuffles (instead of 160): every step
+// halves the number of live values by exchanging one half with the partner lane.  On return
+// v[0] of lane l holds the warp total of value l.
+__device__ __forceinline__ void warp_transpose_sum32(float v[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; i++) {
+      const float send = upper ? v[i] : v[i + off];
+      const float keep = upper ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
 }
 
 // acc += w * (J^T J | -J^T e | 0.5 e^2) for one residual row
@@ -125,7 +168,7 @@ __device__ __forceinline__ float robust_weight(float si, float e, float k) {
 }
 
 template <int KIND>
-__device__ __forceinline__ void point_rows(const TrackArgs &A, const Pose &T, const float X[3],
+__device__ __forceinline__ void point_rows(const TrackArgs &A, const float K[9], const Pose &T, const float X[3],
                                            const float m[4], float s, float acc[kTrAcc]) {
   if (s == 0.0f) return;  // masked point: contributes exact zeros in the reference
   float P[3];
@@ -153,14 +196,14 @@ __device__ __forceinline__ void point_rows(const TrackArgs &A, const Pose &T, co
   } else {
     // geometry.project_calib (geometry.py:64-107)
     const float x = P[0], y = P[1], z = P[2];
-    const float p0 = A.K[0] * x + A.K[1] * y + A.K[2] * z;
-    const float p1 = A.K[3] * x + A.K[4] * y + A.K[5] * z;
-    const float p2 = A.K[6] * x + A.K[7] * y + A.K[8] * z;
+    const float p0 = K[0] * x + K[1] * y + K[2] * z;
+    const float p1 = K[3] * x + K[4] * y + K[5] * z;
+    const float p2 = K[6] * x + K[7] * y + K[8] * z;
     const float u = p0 / p2, v = p1 / p2;
     const bool ok = (u > A.u_lo) && (u < A.u_hi) && (v > A.v_lo) && (v < A.v_hi) && (z > A.z_eps);
     if (!ok) return;
     const float z_inv = 1.0f / z;
-    const float fx = A.K[0], fy = A.K[4];
+    const float fx = K[0], fy = K[4];
     const float sa = s * A.inv_sigma_a, sb = s * A.inv_sigma_b;
     const float a0[3] = {fx * z_inv, 0.0f, -fx * x * z_inv * z_inv};
     const float a1[3] = {0.0f, fy * z_inv, -fy * y * z_inv * z_inv};
@@ -208,12 +251,18 @@ __global__ void __launch_bounds__(kTrThreads, 1) track_pose_kernel(const TrackAr
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TrackSmem &S = *reinterpret_cast<TrackSmem *>(smem_raw);
   float *rec = reinterpret_cast<float *>(smem_raw + ((sizeof(TrackSmem) + 15) & ~size_t(15)));
-  cg::grid_group grid = cg::this_grid();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = gridDim.x;
   const int chunk = (A.n + G - 1) / G;
   const int c0 = min(blockIdx.x * chunk, A.n), c1 = min(c0 + chunk, A.n);
   const int cnt = c1 - c0;
+  // counter value when this launch started: written by the previous launch's last action
+  const unsigned base = __ldcg(A.barrier + 1);
+  float K[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (KIND == M3R_GN_CALIB) {
+#pragma unroll
+    for (int k = 0; k < 9; k++) K[k] = __ldg(A.Kp + k);
+  }
 
   if (STAGED) {
     // structure of arrays with stride `chunk`: conflict-free in the iteration loop
@@ -249,15 +298,18 @@ __global__ void __launch_bounds__(kTrThreads, 1) track_pose_kernel(const TrackAr
       } else {
         load_point<KIND>(A, c0 + k, X, m, s);
       }
-      point_rows<KIND>(A, T, X, m, s, acc);
+      point_rows<KIND>(A, K, T, X, m, s, acc);
     }
-    // warp: fp32 butterfly; CTA and grid: fp64 in a fixed order
+    // warp: fp32 shuffles; CTA and grid: fp64 in a fixed order
+    {
+      float tail[4] = {acc[32], acc[33], acc[34], acc[35]};
 #pragma unroll
-    for (int k = 0; k < kTrAcc; k++) {
-      float v = acc[k];
+      for (int k = 0; k < 4; k++)
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) S.warp_part[warp][k] = static_cast<double>(v);
+        for (int o = 16; o > 0; o >>= 1) tail[k] += __shfl_xor_sync(0xffffffffu, tail[k], o);
+      warp_transpose_sum32(acc, lane);
+      S.warp_part[warp][lane] = static_cast<double>(acc[0]);
+      if (lane < 4) S.warp_part[warp][32 + lane] = static_cast<double>(tail[lane]);
     }
     __syncthreads();
     double *part = A.partial + static_cast<size_t>(it & 1) * G * kTrAcc;
@@ -267,12 +319,15 @@ __global__ void __launch_bounds__(kTrThreads, 1) track_pose_kernel(const TrackAr
       for (int w = 0; w < kTrWarps; w++) v += S.warp_part[w][tid];
       part[static_cast<size_t>(blockIdx.x) * kTrAcc + tid] = v;
     }
-    grid.sync();
-    // every CTA: the same ordered sum over the G partials (8 interleaved slices per value)
+    grid_barrier(A.barrier, base + static_cast<unsigned>(it + 1) * G);
+    // every CTA: pull all G partials into shared memory (independent coalesced L2 loads), then
+    // the same ordered sum on every CTA (8 interleaved slices per value)
+    for (int k = tid; k < G * kTrAcc; k += kTrThreads) S.all_part[k] = __ldcg(part + k);
+    __syncthreads();
     if (tid < kTrAcc * 8) {
       const int v = tid >> 3, sl = tid & 7;
       double s = 0.0;
-      for (int c = sl; c < G; c += 8) s += __ldcg(part + static_cast<size_t>(c) * kTrAcc + v);
+      for (int c = sl; c < G; c += 8) s += S.all_part[c * kTrAcc + v];
       s += __shfl_xor_sync(0xffffffffu, s, 1);
       s += __shfl_xor_sync(0xffffffffu, s, 2);
       s += __shfl_xor_sync(0xffffffffu, s, 4);
@@ -320,6 +375,8 @@ __global__ void __launch_bounds__(kTrThreads, 1) track_pose_kernel(const TrackAr
     R->T_CkCf[0] = Tc.t[0], R->T_CkCf[1] = Tc.t[1], R->T_CkCf[2] = Tc.t[2];
     R->T_CkCf[3] = Tc.q[0], R->T_CkCf[4] = Tc.q[1], R->T_CkCf[5] = Tc.q[2], R->T_CkCf[6] = Tc.q[3];
     R->T_CkCf[7] = Tc.s;
+    // every CTA has passed `it` barriers and read `base` long ago: safe to publish the new base
+    A.barrier[1] = base + static_cast<unsigned>(it) * G;
     R->status = S.stop == 2 ? M3R_TRACK_CHOLESKY_FAILED : M3R_TRACK_OK;
     R->iterations = it;
     R->cost = S.cost;
@@ -349,12 +406,12 @@ static int launch_track(const TrackArgs &A, int grid, size_t smem, cudaStream_t 
 
 using namespace m3r;
 
-extern "C" int64_t m3r_track_scratch_doubles(void) { return 2LL * kTrMaxGrid * kTrAcc; }
+extern "C" int64_t m3r_track_scratch_doubles(void) { return 2 + 2LL * kNumSMs * kTrAcc; }
 
 extern "C" int m3r_track_pose(const m3r_track_params *prm, const float *Xf, int64_t n_f,
                               const int64_t *idx_f2k, const float *Xk, const float *Qk,
                               const uint8_t *valid, const float *meas_k, const uint8_t *valid_meas_k,
-                              int64_t n, const float *T_WCf, const float *T_WCk,
+                              const float *K, int64_t n, const float *T_WCf, const float *T_WCk,
                               m3r_track_result *result, double *scratch, void *stream) {
   M3R_REQUIRE(prm && result && scratch && T_WCf && T_WCk, "track_pose: null pointer");
   M3R_REQUIRE(prm->kind == M3R_GN_RAYS || prm->kind == M3R_GN_CALIB,
@@ -365,18 +422,17 @@ extern "C" int m3r_track_pose(const m3r_track_params *prm, const float *Xf, int6
   M3R_REQUIRE(prm->max_iters >= 1, "track_pose: max_iters must be >= 1");
   M3R_REQUIRE(prm->sigma_a > 0.0f && prm->sigma_b > 0.0f, "track_pose: sigmas must be positive");
   if (prm->kind == M3R_GN_RAYS) M3R_REQUIRE(Xk != nullptr, "track_pose: rays need Xk");
-  else M3R_REQUIRE(meas_k && valid_meas_k, "track_pose: calib needs meas_k and valid_meas_k");
+  else M3R_REQUIRE(meas_k && valid_meas_k && K, "track_pose: calib needs meas_k, valid_meas_k and K");
   M3R_REQUIRE((reinterpret_cast<uintptr_t>(T_WCf) & 15u) == 0 && (reinterpret_cast<uintptr_t>(T_WCk) & 15u) == 0,
               "track_pose: poses must be 16-byte aligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   TrackArgs A{};
   A.Xf = Xf, A.idx = reinterpret_cast<const long long *>(idx_f2k), A.Xk = Xk, A.Qk = Qk, A.valid = valid;
   A.meas = meas_k, A.valid_meas = valid_meas_k, A.T_WCf = T_WCf, A.T_WCk = T_WCk;
-  A.result = result, A.partial = scratch;
+  A.result = result, A.partial = scratch + 2, A.barrier = reinterpret_cast<unsigned *>(scratch), A.Kp = K;
   A.n = static_cast<int>(n), A.n_f = static_cast<int>(n_f), A.max_iters = prm->max_iters;
   A.inv_sigma_a = 1.0f / prm->sigma_a, A.inv_sigma_b = 1.0f / prm->sigma_b;
   A.huber_k = prm->huber_k, A.rel_error = prm->rel_error, A.delta_norm = prm->delta_norm;
-  for (int k = 0; k < 9; k++) A.K[k] = prm->K[k];
   // geometry.py:79-80: u > border && u < w - 1 - border (and v with h)
   A.u_lo = prm->pixel_border, A.u_hi = static_cast<float>(prm->width - 1) - prm->pixel_border;
   A.v_lo = prm->pixel_border, A.v_hi = static_cast<float>(prm->height - 1) - prm->pixel_border;

@@ -70,7 +70,6 @@ class TrackParams(ctypes.Structure):
         ("huber_k", c_float),
         ("sigma_a", c_float),
         ("sigma_b", c_float),
-        ("K", c_float * 9),
         ("height", c_int),
         ("width", c_int),
         ("pixel_border", c_float),
@@ -130,7 +129,7 @@ track_scratch_doubles = _sig("m3r_track_scratch_doubles", c_int64, [])
 track_pose = _sig(
     "m3r_track_pose",
     c_int,
-    [ctypes.POINTER(TrackParams), c_void_p, c_int64] + [c_void_p] * 6 + [c_int64] + [c_void_p] * 5,
+    [ctypes.POINTER(TrackParams), c_void_p, c_int64] + [c_void_p] * 7 + [c_int64] + [c_void_p] * 5,
 )
 
 gn_workspace_create = _sig("m3r_gn_workspace_create", c_int, [ctypes.POINTER(c_void_p)])

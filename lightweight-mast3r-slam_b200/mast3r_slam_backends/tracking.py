@@ -93,6 +93,7 @@ def _solve(kind, Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_s
     prm.max_iters = int(cfg["max_iters"])
     prm.rel_error, prm.delta_norm, prm.huber_k = float(cfg["rel_error"]), float(cfg["delta_norm"]), float(cfg["huber"])
     if kind == _lib.GN_RAYS:
+        K = None
         Xk = _f32("Xk", Xk, ((3,),))
         if Xk.shape[0] != n:
             raise RuntimeError("Xk and Qk must have the same number of points")
@@ -103,20 +104,18 @@ def _solve(kind, Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_s
         if meas_k.shape[0] != n:
             raise RuntimeError("meas_k and Qk must have the same number of points")
         prm.sigma_a, prm.sigma_b = float(cfg["sigma_pixel"]), float(cfg["sigma_depth"])
-        Kh = K.detach().to("cpu", torch.float32).reshape(9).tolist()
-        for i in range(9):
-            prm.K[i] = Kh[i]
+        K = _f32("K", K.reshape(1, 9), ((9,),))
         prm.height, prm.width = int(img_size[0]), int(img_size[1])
         prm.pixel_border, prm.z_eps = float(cfg["pixel_border"]), float(cfg["depth_eps"])
         Xk = None
     key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
     if key not in _scratch:
-        _scratch[key] = torch.empty(_lib.track_scratch_doubles(), dtype=torch.float64, device=dev)
+        _scratch[key] = torch.zeros(_lib.track_scratch_doubles(), dtype=torch.float64, device=dev)
     result = torch.empty(ctypes.sizeof(_lib.TrackResult), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         rc = _lib.track_pose(
             ctypes.byref(prm), _ptr(Xf), Xf.shape[0], _ptr(idx_f2k), _ptr(Xk), _ptr(Qk), _ptr(valid),
-            _ptr(meas_k), _ptr(valid_meas_k), n, _ptr(T_WCf), _ptr(T_WCk), _ptr(result),
+            _ptr(meas_k), _ptr(valid_meas_k), _ptr(K), n, _ptr(T_WCf), _ptr(T_WCk), _ptr(result),
             _ptr(_scratch[key]), _stream(),
         )
     _lib.check(rc, "track_pose")
