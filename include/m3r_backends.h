@@ -122,6 +122,30 @@ int m3r_match(const float *X11, const float *X21, const void *D11, const void *D
               int dilation_max, void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Match confidences and fractions -- replaces the torch gathers and
+ * reductions that follow every match: `Qk = sqrt(Qff[idx_f2k] * Qkf)`, `valid_opt`,
+ * `valid_kf`, `match_frac`, `match_frac_k`, `unique_frac_f` (mast3r_slam/tracker.py:41,
+ * 59-67, 104-110) and `Qj = sqrt(Qii[batch_inds, idx_i2j] * Qji)`, `valid_j`,
+ * `match_frac_j` (mast3r_slam/global_opt.py:55-68), one pass over idx.
+ *   idx         [b,n]     i64   match index into the source view (n_src points per batch row)
+ *   Q_src       [b,n_src] f32   gathered through idx;  Q_dst [b,n] f32
+ *   valid_match [b,n]     u8
+ *   C_src       [b,n_src] f32 or NULL, C_dst [b,n] f32 or NULL   averaged confidences
+ *   Q_out       [b,n]     f32   sqrt(Q_src[idx] * Q_dst), bit-identical to torch
+ *   valid_q     [b,n]     u8    valid_match && Q > Q_conf
+ *   valid_opt   [b,n]     u8 or NULL (with C): valid_q && C_src[idx] > C_conf && C_dst > C_conf
+ *   counts      [b,3]     i32   sum(valid_q), sum(valid_opt), #distinct idx among valid_match
+ *   scratch     m3r_match_confidence_scratch_bytes(b, n_src) bytes, or NULL to skip the
+ *               distinct count (counts[:,2] = 0)
+ * ------------------------------------------------------------------------------------- */
+int64_t m3r_match_confidence_scratch_bytes(int b, int n_src);
+int m3r_match_confidence(const int64_t *idx, const float *Q_src, const float *Q_dst,
+                         const uint8_t *valid_match, const float *C_src, const float *C_dst,
+                         float Q_conf, float C_conf, float *Q_out, uint8_t *valid_q,
+                         uint8_t *valid_opt, int32_t *counts, void *scratch, int b, int n, int n_src,
+                         void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * Tracking pose solve -- replaces the bodies of
  * `FrameTracker.opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid)` and
  * `FrameTracker.opt_pose_calib_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K,

@@ -301,6 +301,68 @@ __global__ void pixel_to_lin_kernel(const long long *__restrict__ p1, long long 
   lin[k] = p.x + static_cast<long long>(w) * p.y;
 }
 
+
+// match_confidence: the gathers and reductions that follow every match:
+// tracker.py:41,62-67,104-110 and global_opt.py:55-68.  One pass over idx produces
+//   Q      = sqrt(Q_src[idx] * Q_dst)                       (bit-identical to torch's mul + sqrt)
+//   valid_q   = valid_match & (Q > Q_conf)                  ("valid_kf" / "valid_j")
+//   valid_opt = valid_q & (C_src[idx] > C_conf) & (C_dst > C_conf)      (when C given)
+// and the three integer counts the callers turn into fractions: sum(valid_q), sum(valid_opt)
+// and the number of distinct idx among valid_match (torch.unique(...).shape[0], counted with a
+// first-setter-wins bitmap instead of a sort).
+constexpr int kMcThreads = 256;
+
+__global__ void __launch_bounds__(kMcThreads)
+    match_confidence_kernel(const long long *__restrict__ idx, const float *__restrict__ Q_src,
+                            const float *__restrict__ Q_dst, const uint8_t *__restrict__ valid_match,
+                            const float *__restrict__ C_src, const float *__restrict__ C_dst,
+                            float Q_conf, float C_conf, float *__restrict__ Q_out,
+                            uint8_t *__restrict__ valid_q, uint8_t *__restrict__ valid_opt,
+                            int *__restrict__ counts, unsigned *__restrict__ bitmap, int n, int n_src,
+                            int bitmap_words) {
+  const int b = blockIdx.y;
+  const size_t row = static_cast<size_t>(b) * n, srow = static_cast<size_t>(b) * n_src;
+  int c_q = 0, c_opt = 0, c_uni = 0;
+  for (int k = blockIdx.x * kMcThreads + threadIdx.x; k < n; k += gridDim.x * kMcThreads) {
+    long long j = idx[row + k];
+    const bool vm = valid_match[row + k] != 0;
+    const bool inb = j >= 0 && j < n_src;
+    if (!inb) j = 0;
+    const float q = sqrtf(__ldg(Q_src + srow + j) * __ldg(Q_dst + row + k));
+    const bool vq = vm && (q > Q_conf);
+    Q_out[row + k] = q;
+    valid_q[row + k] = vq ? 1 : 0;
+    c_q += vq;
+    if (valid_opt) {
+      const bool vo = vq && (__ldg(C_src + srow + j) > C_conf) && (__ldg(C_dst + row + k) > C_conf);
+      valid_opt[row + k] = vo ? 1 : 0;
+      c_opt += vo;
+    }
+    if (bitmap && vm && inb) {
+      const unsigned bit = 1u << (j & 31);
+      const unsigned old = atomicOr(bitmap + static_cast<size_t>(b) * bitmap_words + (j >> 5), bit);
+      c_uni += (old & bit) == 0;
+    }
+  }
+  __shared__ int red[3][kMcThreads / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    c_q += __shfl_xor_sync(0xffffffffu, c_q, o);
+    c_opt += __shfl_xor_sync(0xffffffffu, c_opt, o);
+    c_uni += __shfl_xor_sync(0xffffffffu, c_uni, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = c_q, red[1][threadIdx.x >> 5] = c_opt, red[2][threadIdx.x >> 5] = c_uni;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    int v = 0;
+#pragma unroll
+    for (int w = 0; w < kMcThreads / 32; w++) v += red[threadIdx.x][w];
+    if (v) atomicAdd(counts + b * 3 + threadIdx.x, v);  // integers: order does not matter
+  }
+}
+
 // =========================================================================================
 // refine_matches
 // =========================================================================================
@@ -896,5 +958,36 @@ extern "C" int m3r_match(const float *X11, const float *X21, const void *D11, co
   pixel_to_lin_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, s>>>(
       p1, reinterpret_cast<long long *>(idx_1_to_2), total, w);
   M3R_LAUNCH_CHECK("pixel_to_lin_kernel");
+  return M3R_OK;
+}
+
+extern "C" int64_t m3r_match_confidence_scratch_bytes(int b, int n_src) {
+  return static_cast<int64_t>(b) * ((n_src + 31) / 32) * 4;
+}
+
+extern "C" int m3r_match_confidence(const int64_t *idx, const float *Q_src, const float *Q_dst,
+                                    const uint8_t *valid_match, const float *C_src, const float *C_dst,
+                                    float Q_conf, float C_conf, float *Q_out, uint8_t *valid_q,
+                                    uint8_t *valid_opt, int32_t *counts, void *scratch, int b, int n,
+                                    int n_src, void *stream) {
+  M3R_REQUIRE(b >= 0 && n >= 0 && n_src >= 0, "match_confidence: negative size");
+  M3R_REQUIRE(counts != nullptr, "match_confidence: null counts");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (b == 0) return M3R_OK;
+  M3R_CUDA_TRY(cudaMemsetAsync(counts, 0, sizeof(int32_t) * 3 * b, s));
+  if (n == 0) return M3R_OK;
+  M3R_REQUIRE(idx && Q_src && Q_dst && valid_match && Q_out && valid_q, "match_confidence: null pointer");
+  M3R_REQUIRE(n_src >= 1, "match_confidence: empty source view");
+  M3R_REQUIRE((valid_opt == nullptr) == (C_src == nullptr) && (C_src == nullptr) == (C_dst == nullptr),
+              "match_confidence: C_src, C_dst and valid_opt go together");
+  M3R_REQUIRE(b <= 65535, "match_confidence: batch %d exceeds grid.y limit", b);
+  const int words = (n_src + 31) / 32;
+  if (scratch) M3R_CUDA_TRY(cudaMemsetAsync(scratch, 0, static_cast<size_t>(b) * words * 4, s));
+  int gx = (n + kMcThreads - 1) / kMcThreads;
+  if (gx > kNumSMs * 8) gx = kNumSMs * 8;
+  match_confidence_kernel<<<dim3(gx, b), kMcThreads, 0, s>>>(
+      reinterpret_cast<const long long *>(idx), Q_src, Q_dst, valid_match, C_src, C_dst, Q_conf, C_conf,
+      Q_out, valid_q, valid_opt, counts, static_cast<unsigned *>(scratch), n, n_src, words);
+  M3R_LAUNCH_CHECK("match_confidence_kernel");
   return M3R_OK;
 }

@@ -125,6 +125,12 @@ match = _sig(
     c_int,
     [c_void_p] * 4 + [c_int] * 2 + [c_void_p] * 5 + [c_int] * 4 + [c_float] * 3 + [c_int] * 2 + [c_void_p],
 )
+match_confidence_scratch_bytes = _sig("m3r_match_confidence_scratch_bytes", c_int64, [c_int, c_int])
+match_confidence = _sig(
+    "m3r_match_confidence",
+    c_int,
+    [c_void_p] * 6 + [c_float] * 2 + [c_void_p] * 5 + [c_int] * 3 + [c_void_p],
+)
 track_scratch_doubles = _sig("m3r_track_scratch_doubles", c_int64, [])
 track_pose = _sig(
     "m3r_track_pose",
@@ -189,6 +195,8 @@ EXPORTS = [
     "m3r_refine_matches_v",
     "m3r_prep_rays",
     "m3r_match",
+    "m3r_match_confidence_scratch_bytes",
+    "m3r_match_confidence",
     "m3r_track_scratch_doubles",
     "m3r_track_pose",
     "m3r_gn_workspace_create",

@@ -142,3 +142,54 @@ def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None):
 def match(X11, X21, D11, D21, idx_1_to_2_init=None):
     """matching.py:8-10"""
     return match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init)
+
+
+def match_confidence(idx, Q_src, Q_dst, valid_match, Q_conf, C_src=None, C_dst=None, C_conf=0.0,
+                     count_unique=False):
+    """The gathers and reductions that follow a match, one kernel.
+
+    idx [b,n] i64; Q_src [b,n_src,(1)], Q_dst [b,n,(1)] f32; valid_match [b,n,(1)] bool;
+    optional averaged confidences C_src [b,n_src,(1)], C_dst [b,n,(1)].
+    Returns (Q [b,n,1], valid_q [b,n,1] bool, valid_opt [b,n,1] bool or None, counts [b,3] i32)
+    with counts = (sum valid_q, sum valid_opt, number of distinct idx among valid_match).
+
+    tracker.py:41,59-67,104-110 (b = 1):
+        Qk, valid_kf, valid_opt, c = match_confidence(idx_f2k[None], Qff[None], Qkf[None], ...)
+        match_frac = c[0,1] / n;  match_frac_k = c[0,0] / n;  unique_frac_f = c[0,2] / n
+    global_opt.py:55-68:
+        Qj, valid_j, _, c = match_confidence(idx_i2j, Qii, Qji, valid_match_j, Q_conf)
+        match_frac_j = c[:,0] / n
+    """
+    if not idx.is_cuda or idx.dtype != torch.int64 or idx.dim() != 2:
+        raise RuntimeError("match_confidence: idx must be a CUDA int64 tensor of shape [b,n]")
+    b, n = idx.shape
+    dev = idx.device
+    Qs, Qd = Q_src.reshape(b, -1), Q_dst.reshape(b, -1)
+    _need_cuda_f32(Q_src=Qs, Q_dst=Qd)
+    n_src = Qs.shape[1]
+    vm = valid_match.reshape(b, -1)
+    if not vm.is_cuda or vm.dtype not in (torch.bool, torch.uint8) or vm.shape[1] != n or Qd.shape[1] != n:
+        raise RuntimeError("match_confidence: valid_match / Q_dst must be CUDA tensors with n entries per row")
+    Cs = Cd = None
+    if C_src is not None or C_dst is not None:
+        if C_src is None or C_dst is None:
+            raise RuntimeError("match_confidence: C_src and C_dst go together")
+        Cs, Cd = C_src.reshape(b, -1).contiguous(), C_dst.reshape(b, -1).contiguous()
+        _need_cuda_f32(C_src=Cs, C_dst=Cd)
+        if Cs.shape[1] != n_src or Cd.shape[1] != n:
+            raise RuntimeError("match_confidence: C_src / C_dst have the wrong number of points")
+    idx, Qs, Qd, vm = idx.contiguous(), Qs.contiguous(), Qd.contiguous(), vm.contiguous()
+    Q = torch.empty((b, n, 1), dtype=torch.float32, device=dev)
+    valid_q = torch.empty((b, n, 1), dtype=torch.bool, device=dev)
+    valid_opt = torch.empty((b, n, 1), dtype=torch.bool, device=dev) if Cs is not None else None
+    counts = torch.empty((b, 3), dtype=torch.int32, device=dev)
+    scratch = None
+    if count_unique and b > 0:
+        scratch = torch.empty(max(_lib.match_confidence_scratch_bytes(b, n_src), 4), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.match_confidence(
+            _ptr(idx), _ptr(Qs), _ptr(Qd), _ptr(vm), _ptr(Cs), _ptr(Cd), float(Q_conf), float(C_conf),
+            _ptr(Q), _ptr(valid_q), _ptr(valid_opt), _ptr(counts), _ptr(scratch), b, n, n_src, _stream(),
+        )
+    _lib.check(rc, "match_confidence")
+    return Q, valid_q, valid_opt, counts

@@ -157,3 +157,78 @@ def test_match_errors_and_empty(front):
     own = torch.arange(32 * 48, device="cuda").view(32, 48)
     assert valid.view(32, 48)[2:-2, 2:-2].all()
     assert torch.equal(idx.view(32, 48)[2:-2, 2:-2], own[2:-2, 2:-2])
+
+
+# ------------------------------------------------------------------------- match confidences
+def _confidence_reference(idx, Qs, Qd, vm, Q_conf, Cs=None, Cd=None, C_conf=0.0):
+    """The reference's torch lines, verbatim in structure: tracker.py:41,59-67,104-110 and
+    global_opt.py:52-68 (batched gather through batch_inds)."""
+    b, n = idx.shape
+    batch_inds = torch.arange(b, device=idx.device)[:, None].repeat(1, n)
+    Q = torch.sqrt(Qs[batch_inds, idx] * Qd)
+    valid_q = vm & (Q > Q_conf)
+    valid_opt = None
+    if Cs is not None:
+        valid_opt = vm & (Cs[batch_inds, idx] > C_conf) & (Cd > C_conf) & (Q > Q_conf)
+    uniq = [torch.unique(idx[i][vm[i, :, 0]]).shape[0] for i in range(b)]
+    return Q, valid_q, valid_opt, uniq
+
+
+@pytest.mark.parametrize("b,n,n_src,with_c", [(1, 196608, 196608, True), (4, 50176, 50176, False),
+                                              (3, 1000, 777, True), (1, 5, 9, True)])
+def test_match_confidence_bit_exact(front, b, n, n_src, with_c):
+    g = torch.Generator(device="cuda").manual_seed(b * 131 + n)
+    idx = torch.randint(0, n_src, (b, n), generator=g, device="cuda")
+    idx[:, : n // 3] = idx[:, :1]  # many duplicates
+    Qs = torch.exp(1.0 + 0.5 * torch.randn(b, n_src, 1, generator=g, device="cuda"))
+    Qd = torch.exp(1.0 + 0.5 * torch.randn(b, n, 1, generator=g, device="cuda"))
+    vm = torch.rand(b, n, 1, generator=g, device="cuda") < 0.8
+    Cs = Cd = None
+    if with_c:
+        Cs = torch.randn(b, n_src, 1, generator=g, device="cuda") + 0.5
+        Cd = torch.randn(b, n, 1, generator=g, device="cuda") + 0.5
+    Q, vq, vo, counts = front.match_confidence(idx, Qs, Qd, vm, 1.5, Cs, Cd, 0.0, count_unique=True)
+    Qr, vqr, vor, uniq = _confidence_reference(idx, Qs, Qd, vm, 1.5, Cs, Cd, 0.0)
+    assert torch.equal(Q, Qr) and torch.equal(vq, vqr)  # float path is bit-identical
+    assert counts[:, 0].tolist() == vqr.sum(dim=(1, 2)).tolist()
+    assert counts[:, 2].tolist() == uniq
+    if with_c:
+        assert torch.equal(vo, vor) and counts[:, 1].tolist() == vor.sum(dim=(1, 2)).tolist()
+    else:
+        assert vo is None and counts[:, 1].tolist() == [0] * b
+    # without the distinct count
+    _, _, _, c2 = front.match_confidence(idx, Qs, Qd, vm, 1.5, Cs, Cd, 0.0)
+    assert c2[:, 2].tolist() == [0] * b and torch.equal(c2[:, :2], counts[:, :2])
+
+
+def test_match_confidence_tracker_usage(front):
+    """b = 1 exactly as FrameTracker.track uses it, on the synthetic tracking inputs."""
+    t = synth.make_track_inputs(96, 128, seed=4, device="cuda")
+    T = synth.TRACK_DEFAULTS
+    Qk, valid_kf, valid_opt, c = front.match_confidence(
+        t["idx_f2k"][None], t["Qff"][None], t["Qkf"][None], t["valid_match_k"][None], T["Q_conf"],
+        t["Cf_canon"][None], t["Ck"][None], T["C_conf"], count_unique=True)
+    assert torch.equal(Qk[0], t["Qk"]) and torch.equal(valid_opt[0], t["valid_opt"])
+    assert torch.equal(valid_kf[0], t["valid_match_k"] & (t["Qk"] > T["Q_conf"]))
+    n = t["n"]
+    assert c[0, 1].item() == int(t["valid_opt"].sum()) and c[0, 0].item() == int(valid_kf.sum())
+    assert c[0, 2].item() == torch.unique(t["idx_f2k"][t["valid_match_k"][:, 0]]).shape[0]
+    assert 0 < c[0, 1].item() / n < 1
+
+
+def test_match_confidence_errors(front):
+    idx = torch.zeros(1, 8, dtype=torch.int64, device="cuda")
+    Q = torch.ones(1, 8, 1, device="cuda")
+    vm = torch.ones(1, 8, 1, dtype=torch.bool, device="cuda")
+    with pytest.raises(RuntimeError):
+        front.match_confidence(idx.int(), Q, Q, vm, 1.5)
+    with pytest.raises(RuntimeError):
+        front.match_confidence(idx, Q, Q, vm, 1.5, C_src=Q)
+    with pytest.raises(RuntimeError):
+        front.match_confidence(idx, Q, Q[:, :4], vm, 1.5)
+    # out-of-range indices do not fault and never count as matches of a distinct source point
+    bad = idx.clone()
+    bad[0, 0], bad[0, 1] = -5, 99
+    _, _, _, c = front.match_confidence(bad, Q, Q, vm, 0.5, count_unique=True)
+    torch.cuda.synchronize()
+    assert c[0, 2].item() == 1
