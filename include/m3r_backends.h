@@ -201,6 +201,31 @@ int m3r_track_pose(const m3r_track_params *params, const float *Xf, int64_t n_f,
                    void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Pointmap producers.
+ *
+ * m3r_update_pointmap replaces the in-place fusion branches of `Frame.update_pointmap(X, C)`
+ * (mast3r_slam/frame.py:41-102; the `first` / `recent` / `best_score` branches are plain
+ * copies decided on the host and stay there), optionally preceded by the Sim(3) transport
+ * `Xkk = T_CkCf.act(Xkf)` of mast3r_slam/tracker.py:97-98 when T != NULL -- T may point
+ * straight at `m3r_track_result.T_CkCf`, so no host round trip sits between the pose solve
+ * and the keyframe update.  weighted_pointmap and indep_conf are bit-identical to torch.
+ *   X_canon [n,3] f32 in/out, C_canon [n] f32 in/out (the running SUM of confidences, frame.py:76)
+ *   X [n,3] f32, C [n] f32 the new observation;  T [8] f32 or NULL, 16-byte aligned
+ *
+ * m3r_constrain_points_to_ray replaces `constrain_points_to_ray(img_size, Xs, K)`
+ * (mast3r_slam/geometry.py:37-42 with backproject :107-115 and get_pixel_coords :118-123):
+ * X <- z * ((u - cx)/fx, (v - cy)/fy, 1).  Xs, out [b,h,w,3] f32 (out may alias Xs); K [3,3]
+ * f32 on the device.  Bit-identical to torch.
+ * ------------------------------------------------------------------------------------- */
+#define M3R_FILTER_WEIGHTED_POINTMAP 0  /* frame.py:74-77 */
+#define M3R_FILTER_WEIGHTED_SPHERICAL 1 /* frame.py:78-101 */
+#define M3R_FILTER_INDEP_CONF 2         /* frame.py:69-73 */
+int m3r_update_pointmap(int mode, float *X_canon, float *C_canon, const float *X, const float *C,
+                        const float *T, int64_t n, void *stream);
+int m3r_constrain_points_to_ray(const float *Xs, float *out, const float *K, int b, int h, int w,
+                                void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * Gauss-Newton on the Sim(3) keyframe graph.
  *
  * A workspace caches device scratch (per-edge blocks, the assembled system, index maps)

@@ -6,7 +6,7 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SRC = [os.path.join(HERE, "csrc", f) for f in ("common.cu", "matching.cu", "tracking.cu", "gn.cu")]
+SRC = [os.path.join(HERE, "csrc", f) for f in ("common.cu", "matching.cu", "tracking.cu", "pointmap.cu", "gn.cu")]
 OUT = os.path.join(HERE, "libm3r_b200.so")
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

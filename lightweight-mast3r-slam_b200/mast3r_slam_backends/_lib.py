@@ -137,6 +137,11 @@ track_pose = _sig(
     c_int,
     [ctypes.POINTER(TrackParams), c_void_p, c_int64] + [c_void_p] * 7 + [c_int64] + [c_void_p] * 5,
 )
+update_pointmap = _sig("m3r_update_pointmap", c_int, [c_int] + [c_void_p] * 5 + [c_int64, c_void_p])
+constrain_points_to_ray = _sig(
+    "m3r_constrain_points_to_ray", c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]
+)
+FILTER_MODES = {"weighted_pointmap": 0, "weighted_spherical": 1, "indep_conf": 2}
 
 gn_workspace_create = _sig("m3r_gn_workspace_create", c_int, [ctypes.POINTER(c_void_p)])
 gn_workspace_destroy = _sig("m3r_gn_workspace_destroy", None, [c_void_p])
@@ -199,6 +204,8 @@ EXPORTS = [
     "m3r_match_confidence",
     "m3r_track_scratch_doubles",
     "m3r_track_pose",
+    "m3r_update_pointmap",
+    "m3r_constrain_points_to_ray",
     "m3r_gn_workspace_create",
     "m3r_gn_workspace_destroy",
     "m3r_gauss_newton_rays",

@@ -1,3 +1,3 @@
 set -x
-timeout 900 python -m pytest tests/test_front_gpu.py -m gpu -q -x > gpurun_out/pytest_front.log 2>&1; echo "pytest rc=$?"
-tail -15 gpurun_out/pytest_front.log
+timeout 900 python -m pytest tests/test_pointmap_gpu.py -m gpu -q > gpurun_out/pytest_pm.log 2>&1; echo "pytest rc=$?"
+tail -25 gpurun_out/pytest_pm.log
