@@ -338,6 +338,48 @@ def time_front_e2e(sets, M, steps, warmup, world):
             "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
 
 
+def time_frame_pipeline(sets, M, steps, warmup):
+    """BASELINE config 2 as a whole, the geometric part of FrameTracker.track (tracker.py:29-112)
+    for one 512x384 frame: match -> confidences/fractions -> pose solve -> keyframe pointmap
+    update with the solved relative pose.  Six launches, no host synchronisation in between
+    (the pose travels from the solve to the update in device memory)."""
+    import synth
+    from mast3r_slam_backends import _lib, matching as front, pointmaps, tracking as tr
+
+    T = synth.TRACK_DEFAULTS
+    front.set_config({"matching": dict(M)})
+    tr.set_config({"tracking": dict(T)})
+    t = synth.make_track_inputs(H, W, seed=3, device="cuda", pose_noise=0.03)
+    Xk_canon, Ck_sum = t["Xk"].clone(), t["Ck"].clone()
+    Xkf, Ckf = t["Xk"].clone(), t["Ck"].clone()
+
+    def frame(i):
+        X11, X21 = FRONT_INPUTS[i % len(FRONT_INPUTS)]
+        s = sets[i % len(FRONT_INPUTS)]
+        idx, valid = front.match(X11, X21, s["D11"], s["D21"])
+        Qk, valid_kf, valid_opt, counts = front.match_confidence(
+            idx, t["Qff"][None], t["Qkf"][None], valid, T["Q_conf"], t["Cf_canon"][None], t["Ck"][None],
+            T["C_conf"], count_unique=True)
+        T_WCf, T_CkCf = tr.opt_pose_ray_dist_sim3(t["Xf_canon"], t["Xk"], t["T_WCf_init"], t["T_WCk"], Qk[0],
+                                                  valid_opt[0], idx_f2k=idx[0], check=False)
+        pointmaps.update_pointmap(Xk_canon, Ck_sum, Xkf, Ckf, "weighted_pointmap", T=T_CkCf)
+        return counts
+
+    for i in range(warmup):
+        frame(i)
+    torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(steps):
+        frame(i)
+    t1.record()
+    torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / steps
+    return {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "gpu_launches_per_frame": (_lib.launch_count() - l0) / steps,
+            "stages": "match(3) + match_confidence(1) + track_pose(1) + update_pointmap(1); memsets not counted"}
+
+
 def time_tracking(steps, warmup, cpu=True):
     """The per-frame pose solve of BASELINE config 2 (tracker.py:173-266) at
     512x384: one cooperative launch per call.  `us_per_iter` comes from a fixed-iteration run
@@ -687,6 +729,7 @@ def main():
             line["front_end"]["e2e"] = fe
     if rank == 0 and not args.profile:
         line["tracking"] = time_tracking(max(args.steps // 4, 10), 3)
+        line["frame_pipeline"] = time_frame_pipeline(sets, M, max(args.steps // 2, 20), 3)
 
     # ---- Gauss-Newton
     g = None

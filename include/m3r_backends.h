@@ -111,7 +111,8 @@ int m3r_refine_matches_v(const void *D11, const void *D21, const int64_t *p1, in
  *   idx_init   [b,n] i64 or NULL   previous idx_1_to_2 (NULL = identity, matching.py:41-44)
  *   idx_1_to_2 [b,n] i64           out: u + w*v of the refined pixel
  *   valid      [b,n] u8            out: converged && |X11[p1] - X21| < dist_thresh
- *   rays_ws    b*h*w*9 floats      caller-owned scratch (holds rays_img_with_grad on return)
+ *   rays_ws    b*h*w*12 floats     caller-owned scratch, 16-byte aligned (the ray image in an
+ *                                  internal 48-byte-texel layout read with 128-bit loads)
  *   p1_ws      2*b*n*2 int64       caller-owned scratch, 16-byte aligned
  * ------------------------------------------------------------------------------------- */
 int m3r_prep_rays(const float *X11, float *rays_img_with_grad, int b, int h, int w, void *stream);

@@ -91,6 +91,24 @@ struct GlobalFetch {
   }
 };
 
+// The same gather from the padded image the fused front end writes for itself (48-byte texels:
+// ray, d/du, d/dv, 3 floats of padding): three 128-bit loads per texel instead of nine 32-bit
+// ones (the `lg_throttle` stall of the 9-float path: 36 load instructions per evaluation).
+struct PaddedFetch {
+  const float4 *img;
+  int w;
+  template <int NC>
+  __device__ __forceinline__ void operator()(int uu, int vv, float *out) const {
+    const float4 *s = img + (static_cast<size_t>(vv) * w + uu) * 3;
+    const float4 a = __ldg(s), b = __ldg(s + 1);
+    out[0] = a.x, out[1] = a.y, out[2] = a.z;
+    if (NC > 3) {
+      const float4 c = __ldg(s + 2);
+      out[3] = a.w, out[4] = b.x, out[5] = b.y, out[6] = b.z, out[7] = b.w, out[8] = c.x;
+    }
+  }
+};
+
 // 2x2 normal equations with the LM diagonal and the clamped trial pixel (:202-222)
 __device__ __forceinline__ void lm_step(const float gx[3], const float gy[3], const float err[3],
                                         float lambda, float u, float v, float u_hi, float v_hi,
@@ -111,7 +129,8 @@ __device__ __forceinline__ void lm_step(const float gx[3], const float gy[3], co
 
 // The memoised LM loop (MODE 0 of iter_proj_kernel, see below), shared with the fused match
 // kernel.
-__device__ __forceinline__ void iter_proj_memo(const GlobalFetch &fetch, const float pt[3], float &u,
+template <typename Fetch>
+__device__ __forceinline__ void iter_proj_memo(const Fetch &fetch, const float pt[3], float &u,
                                                float &v, float u_hi, float v_hi, int max_iter,
                                                float lambda_init, float cost_thresh, bool &conv) {
   auto f9 = [&](int uu, int vv, float *out) { fetch.template operator()<9>(uu, vv, out); };
@@ -229,6 +248,7 @@ __device__ __forceinline__ int reflect_idx(int i, int n) {  // F.pad(mode="refle
   return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
 }
 
+template <bool PADDED>
 __global__ void __launch_bounds__(kPrTx * kPrTy)
     prep_rays_kernel(const float *__restrict__ X11, float *__restrict__ rays, int h, int w) {
   __shared__ float tile[kPrTy + 2][kPrTx + 2][3];
@@ -257,9 +277,16 @@ __global__ void __launch_bounds__(kPrTx * kPrTy)
     out[3 + c] = 0.09375f * (a02 - a00) + 0.3125f * (a12 - a10) + 0.09375f * (a22 - a20);
     out[6 + c] = 0.09375f * (a20 - a00) + 0.3125f * (a21 - a01) + 0.09375f * (a22 - a02);
   }
-  float *dst = rays + ((static_cast<size_t>(b) * h + v) * w + u) * 9;
+  if (PADDED) {
+    float4 *dst = reinterpret_cast<float4 *>(rays) + ((static_cast<size_t>(b) * h + v) * w + u) * 3;
+    dst[0] = make_float4(out[0], out[1], out[2], out[3]);
+    dst[1] = make_float4(out[4], out[5], out[6], out[7]);
+    dst[2] = make_float4(out[8], 0.0f, 0.0f, 0.0f);
+  } else {
+    float *dst = rays + ((static_cast<size_t>(b) * h + v) * w + u) * 9;
 #pragma unroll
-  for (int c = 0; c < 9; c++) dst[c] = out[c];
+    for (int c = 0; c < 9; c++) dst[c] = out[c];
+  }
 }
 
 // match_proj: iter_proj with its torch prologue and epilogue folded in (matching.py:38-76):
@@ -275,7 +302,7 @@ __global__ void __launch_bounds__(kIpThreads)
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   const size_t gi = static_cast<size_t>(b) * n + idx;
-  const GlobalFetch fetch{rays + static_cast<size_t>(b) * h * w * 9, w};
+  const PaddedFetch fetch{reinterpret_cast<const float4 *>(rays) + static_cast<size_t>(b) * h * w * 3, w};
   const float X = __ldg(X21 + gi * 3), Y = __ldg(X21 + gi * 3 + 1), Z = __ldg(X21 + gi * 3 + 2);
   const float d = fmaxf(sqrtf(X * X + Y * Y + Z * Z), 1e-12f);
   const float pt[3] = {X / d, Y / d, Z / d};
@@ -910,8 +937,8 @@ extern "C" int m3r_prep_rays(const float *X11, float *rays_img_with_grad, int b,
   M3R_REQUIRE(h >= 2 && w >= 2, "prep_rays: reflect padding needs at least 2x2 (got %dx%d)", h, w);
   M3R_REQUIRE(b <= 65535 && (h + kPrTy - 1) / kPrTy <= 65535, "prep_rays: image or batch too large");
   const dim3 grid((w + kPrTx - 1) / kPrTx, (h + kPrTy - 1) / kPrTy, b);
-  prep_rays_kernel<<<grid, kPrTx * kPrTy, 0, static_cast<cudaStream_t>(stream)>>>(X11, rays_img_with_grad,
-                                                                               h, w);
+  prep_rays_kernel<false><<<grid, kPrTx * kPrTy, 0, static_cast<cudaStream_t>(stream)>>>(
+      X11, rays_img_with_grad, h, w);
   M3R_LAUNCH_CHECK("prep_rays_kernel");
   return M3R_OK;
 }
@@ -929,9 +956,15 @@ extern "C" int m3r_match(const float *X11, const float *X21, const void *D11, co
   M3R_REQUIRE(static_cast<long long>(h) * w < (1LL << 31), "match: image too large");
   M3R_REQUIRE((reinterpret_cast<uintptr_t>(p1_ws) & 15u) == 0, "match: p1_ws must be 16-byte aligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  M3R_REQUIRE(aligned16(rays_ws), "match: rays_ws must be 16-byte aligned");
   const int n = h * w;
-  int rc = m3r_prep_rays(X11, rays_ws, b, h, w, stream);
-  if (rc) return rc;
+  int rc = M3R_OK;
+  {
+    M3R_REQUIRE((h + kPrTy - 1) / kPrTy <= 65535, "match: image too tall");
+    const dim3 pgrid((w + kPrTx - 1) / kPrTx, (h + kPrTy - 1) / kPrTy, b);
+    prep_rays_kernel<true><<<pgrid, kPrTx * kPrTy, 0, s>>>(X11, rays_ws, h, w);  // 12-float texels
+    M3R_LAUNCH_CHECK("prep_rays_kernel");
+  }
   long long *p1 = reinterpret_cast<long long *>(p1_ws);
   long long *p1n = p1 + static_cast<size_t>(b) * n * 2;
   const dim3 grid((n + kIpThreads - 1) / kIpThreads, b);

@@ -126,7 +126,7 @@ def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None):
         idx0 = idx0.contiguous()
     idx_1_to_2 = torch.empty((b, n), dtype=torch.int64, device=dev)
     valid = torch.empty((b, n), dtype=torch.bool, device=dev)
-    rays_ws = torch.empty((b, h, w, 9), dtype=torch.float32, device=dev)
+    rays_ws = torch.empty((b, h, w, 12), dtype=torch.float32, device=dev)
     p1_ws = torch.empty((2, b, n, 2), dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
         rc = _lib.match(
