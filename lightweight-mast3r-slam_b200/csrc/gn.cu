@@ -536,6 +536,9 @@ __global__ void __launch_bounds__(64)
 //   H[a][a] += H_e for every edge touching a;  H[a][b] -= H_e for every edge joining a and b
 //   rhs[a]  += g_e (a = j side) or -g_e (a = i side)
 // ----------------------------------------------------------------------------------------
+constexpr int kAsmMaxStagedEdges = 4096;  // (io, jo) pairs staged in shared memory: 32 KB
+
+template <bool STAGED>
 __global__ void __launch_bounds__(64)
     gn_assemble_kernel(const double *__restrict__ edge_H, const double *__restrict__ edge_g,
                        const int *__restrict__ pose_i, const int *__restrict__ pose_j,
@@ -550,14 +553,25 @@ __global__ void __launch_bounds__(64)
     if (t < 49) sys[static_cast<size_t>(a * 7 + r) * D + (b * 7 + c)] = 0.0;
     return;
   }
+  // the shard's (pose_i, pose_j) pairs: one coalesced pass into shared memory, so that the scan
+  // below costs shared-memory latency per 64-edge tile instead of an L2 round trip
+  extern __shared__ int2 ep[];
+  if (STAGED) {
+    for (int e = t; e < num_shard_edges; e += 64)
+      ep[e] = make_int2(pose_i[edge_begin + e] - 1, pose_j[edge_begin + e] - 1);
+    __syncthreads();
+  }
   __shared__ int hit[64];
   __shared__ int nhit;
+  __shared__ unsigned masks[2];
   double accH = 0.0, accg = 0.0;
   for (int e0 = 0; e0 < num_shard_edges; e0 += 64) {
     const int le = e0 + t;
     int code = 0;  // 1: +H (diag, i side)  2: +H (diag, j side)  3: -H (off-diagonal)
     if (le < num_shard_edges) {
-      const int io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;
+      int io, jo;
+      if (STAGED) io = ep[le].x, jo = ep[le].y;
+      else io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;
       if (a == b) {
         if (io == a && jo == a) code = 0;  // self edge: the four blocks cancel exactly
         else if (io == a) code = 1;
@@ -568,10 +582,13 @@ __global__ void __launch_bounds__(64)
     }
     // compact the hits of this tile in edge order
     const unsigned m0 = __ballot_sync(0xffffffffu, code != 0);
-    __shared__ unsigned masks[2];
     if ((t & 31) == 0) masks[t >> 5] = m0;
     __syncthreads();
     const unsigned lo = masks[0], hi = masks[1];
+    if ((lo | hi) == 0u) {  // no edge of this tile touches the block (the common case)
+      __syncthreads();
+      continue;
+    }
     if (code != 0) {
       const int pos = (t < 32) ? __popc(lo & ((1u << t) - 1u))
                                : __popc(lo) + __popc(hi & ((1u << (t - 32)) - 1u));
@@ -1141,9 +1158,13 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
     M3R_LAUNCH_CHECK("gn_edge_finalize_kernel");
   }
   const int NB = prob->num_poses - 1;
-  gn_assemble_kernel<<<dim3(NB, NB), 64, 0, s>>>(ws->edge_H.p, ws->edge_g.p, ws->pose_i.p,
-                                                 ws->pose_j.p, prob->edge_begin, ES, NB, system,
-                                                 ws->flags);
+  if (ES <= kAsmMaxStagedEdges)
+    gn_assemble_kernel<true><<<dim3(NB, NB), 64, static_cast<size_t>(ES) * sizeof(int2), s>>>(
+        ws->edge_H.p, ws->edge_g.p, ws->pose_i.p, ws->pose_j.p, prob->edge_begin, ES, NB, system, ws->flags);
+  else
+    gn_assemble_kernel<false><<<dim3(NB, NB), 64, 0, s>>>(ws->edge_H.p, ws->edge_g.p, ws->pose_i.p,
+                                                        ws->pose_j.p, prob->edge_begin, ES, NB, system,
+                                                        ws->flags);
   M3R_LAUNCH_CHECK("gn_assemble_kernel");
   return M3R_OK;
 }

@@ -57,6 +57,19 @@ __device__ __forceinline__ double chain_rsqrt(double d) {
   return r;
 }
 
+// 1/d to fp64 accuracy: MUFU.RCP64H seed (~20 bits) and two Newton steps of two dependent FMAs
+// each.  The pivot chain only needs 1/d (to eliminate below the pivot); the square root that
+// scales the column is computed beside it, off the chain.
+__device__ __forceinline__ double chain_rcp(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  return r;
+}
+
 // out-of-line so that the pivot chain's code stays small (never taken for sane systems)
 __device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
 
@@ -75,20 +88,22 @@ __device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *col
     col[lane] = a[j];
     __syncwarp();
     const double d = col[j];
-    double r;
+    double r, rc;
     if (!(d > 0.0)) {
       if (lane == 0) *bad = 1;
-      r = 1.0;  // keep finite; the step is discarded
+      r = 1.0, rc = 1.0;  // keep finite; the step is discarded
     } else if (d < 1e-30 || d > 1e30) {
       r = rsqrt_wide_range(d);
+      rc = r * r;
     } else {
-      r = chain_rsqrt(d);
+      rc = chain_rcp(d);    // on the chain: the next pivot waits for tj
+      r = chain_rsqrt(d);   // beside it: only the stored factor needs the root
     }
-    if (lane == 0) dinv[j] = r;
-    const double tj = a[j] * (r * r);  // A[lane][j] / d
-    a[j] *= r;                         // lane j: sqrt(d); lanes > j: L[lane][j]
+    const double tj = a[j] * rc;  // A[lane][j] / d
 #pragma unroll
     for (int c = j + 1; c < kPB; c++) a[c] -= tj * col[c];  // meaningful for lanes >= c
+    if (lane == 0) dinv[j] = r;
+    a[j] *= r;  // lane j: sqrt(d); lanes > j: L[lane][j]
   }
 }
 
@@ -146,6 +161,7 @@ struct CoopSmem {
   double Ad[kPB][kPB + 1];   // diagonal block with the previous panel's update folded in
   double Ls[kPB][kLs];       // previous panel's L21, rows of the diagonal block
   double dinv[kPB], yk[kPB], bk[kPB], col[kPB];
+  double dpart[64 * 16];     // second half of the diagonal-block update (k = 16..31)
   union {
     struct {
       double Xr[kTrsmRows][kPB + 1];  // this CTA's rows of the panel
@@ -202,6 +218,7 @@ __global__ void __launch_bounds__(kCoopThreads)
       const int row0 = k0 + pb + rc * kTrsmRows;
       const int nrows = max(0, min(kTrsmRows, D - row0));
       // 1. every operand of the panel step in one round of coalesced loads
+#pragma unroll
       for (int x = t; x < kPB * kPB; x += kCoopThreads) {
         const int r = x / kPB, c = x % kPB;
         const size_t g = static_cast<size_t>(k0 + r) * D;
@@ -210,6 +227,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         S.Ad[r][c] = v;
         S.Ls[r][c] = (la && r < pb) ? A[g + kp + c] : 0.0;
       }
+#pragma unroll
       for (int x = t; x < kTrsmRows * kPB; x += kCoopThreads) {
         const int r = x / kPB, c = x % kPB;
         const size_t g = static_cast<size_t>(row0 + r) * D;
@@ -219,18 +237,49 @@ __global__ void __launch_bounds__(kCoopThreads)
       if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
       __syncthreads();
       COOP_ATICK(8);
-      // 2. diagonal block -= Ls Ls^T (all threads, 4 entries each; entries above the diagonal
-      //    receive garbage and are never read)
+      // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
+      //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
+      //    272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner
+      //    dimension; the halves meet in shared memory.  Entries above the diagonal receive
+      //    garbage and are never read.  (The first version gave every thread 4 outputs of one
+      //    row: 5 shared loads per 4 DFMA, 4.2 us per panel on the critical path.)
       if (la) {
-        const int r = t >> 3, c0 = (t & 7) * 4;
-        double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-#pragma unroll 8
-        for (int j = 0; j < kPB; j++) {
-          const double lr = S.Ls[r][j];
-          s0 += lr * S.Ls[c0][j], s1 += lr * S.Ls[c0 + 1][j];
-          s2 += lr * S.Ls[c0 + 2][j], s3 += lr * S.Ls[c0 + 3][j];
+        double acc[4][4];
+        const int tile = t & 63, half = t >> 6;
+        const int tr = tile >> 3, tc = tile & 7;
+        if (t < 128) {
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) acc[i][k] = 0.0;
+#pragma unroll 4
+          for (int j = half * (kPB / 2); j < (half + 1) * (kPB / 2); j += 2) {
+            double2 av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+              av[i] = *reinterpret_cast<const double2 *>(&S.Ls[tr + 8 * i][j]);
+              bv[i] = *reinterpret_cast<const double2 *>(&S.Ls[tc + 8 * i][j]);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+              for (int k = 0; k < 4; k++) acc[i][k] += av[i].x * bv[k].x + av[i].y * bv[k].y;
+          }
         }
-        S.Ad[r][c0] -= s0, S.Ad[r][c0 + 1] -= s1, S.Ad[r][c0 + 2] -= s2, S.Ad[r][c0 + 3] -= s3;
+        if (t >= 64 && t < 128) {
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) S.dpart[(i * 4 + k) * 64 + tile] = acc[i][k];
+        }
+        __syncthreads();
+        if (t < 64) {
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+              S.Ad[tr + 8 * i][tc + 8 * k] -= acc[i][k] + S.dpart[(i * 4 + k) * 64 + tile];
+        }
       }
       __syncthreads();
       COOP_ATICK(9);
@@ -349,9 +398,74 @@ __global__ void __launch_bounds__(kCoopThreads)
   if (blockIdx.x != 0) return;
 
   // ---------------- backward substitution L^T x = y (CTA 0), x overwrites xbuf
+  // The vector lives in shared memory for the whole phase, the diagonal block of the NEXT step
+  // is prefetched by the idle warps while warp 0 walks the current 32-pivot chain, and the
+  // update threads issue their loads of L before the barrier that publishes x_k: per block the
+  // critical path is one chain plus 32 FMAs instead of chain + three L2 round trips.
   __syncthreads();
   const bool fail = bad != 0;
-  if (!fail) {
+  constexpr int kLdBuf = kPB * kPB + kPB;
+  constexpr int kXsCap = kTrsmRows * kLs;  // doubles available in S.u.a.Lp
+  if (!fail && D <= kXsCap) {
+    double *xs = &S.u.a.Lp[0][0];
+    double *ldb = &S.u.a.Xr[0][0];  // 2 x kLdBuf doubles (Xr holds 128 x 33)
+    const int last = ((D - 1) / kPB) * kPB;
+    for (int j = t; j < D; j += kCoopThreads) xs[j] = xbuf[j];
+    for (int x = t; x < kLdBuf; x += kCoopThreads)
+      ldb[x] = ldiag[static_cast<size_t>(last / kPB) * kLdStride + x];
+    __syncthreads();
+    int buf = 0;
+    constexpr int kUpd = kCoopThreads - 32;  // update threads (warps 1..7)
+    for (int k0 = last; k0 >= 0; k0 -= kPB, buf ^= 1) {
+      const int pb = min(kPB, D - k0);
+      double lv[kPB];
+      const int j0 = t - 32;
+      if (warp == 0) {  // x_k = L11^-T y_k
+        const double *Ld = ldb + buf * kLdBuf;
+        double col[kPB];  // column `lane` of L11: col[r] = L11[r][lane]
+#pragma unroll
+        for (int r = 0; r < kPB; r++) col[r] = Ld[r * kPB + lane];
+        const double my_dinv = Ld[kPB * kPB + lane];
+        double mine = (lane < pb) ? xs[k0 + lane] : 0.0;
+#pragma unroll
+        for (int cc = kPB - 1; cc >= 0; cc--) {  // x_cc travels through shared memory
+          if (lane == cc) mine *= my_dinv, yk[cc] = mine;
+          __syncwarp();
+          if (lane < cc) mine -= col[cc] * yk[cc];
+        }
+        __syncwarp();
+        if (lane < pb) xs[k0 + lane] = mine;
+      } else {
+        if (k0 > 0) {
+          const double *src = ldiag + static_cast<size_t>(k0 / kPB - 1) * kLdStride;
+          for (int x = j0; x < kLdBuf; x += kUpd) ldb[(buf ^ 1) * kLdBuf + x] = src[x];
+        }
+        if (j0 < k0) {
+#pragma unroll
+          for (int c = 0; c < kPB; c++)
+            lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j0] : 0.0;
+        }
+      }
+      __syncthreads();
+      // y_j -= sum_c L[k0+c][j] x_k[c] for all j < k0: independent, coalesced rows of L
+      if (warp != 0) {
+        for (int j = j0; j < k0; j += kUpd) {
+          if (j != j0) {
+#pragma unroll
+            for (int c = 0; c < kPB; c++)
+              lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j] : 0.0;
+          }
+          double sacc = xs[j];
+#pragma unroll
+          for (int c = 0; c < kPB; c++) sacc -= lv[c] * yk[c];
+          xs[j] = sacc;
+        }
+      }
+      __syncthreads();
+    }
+    for (int j = t; j < D; j += kCoopThreads) xbuf[j] = xs[j];
+    __syncthreads();
+  } else if (!fail) {
     const int last = ((D - 1) / kPB) * kPB;
     for (int k0 = last; k0 >= 0; k0 -= kPB) {
       const int pb = min(kPB, D - k0);
@@ -372,16 +486,15 @@ __global__ void __launch_bounds__(kCoopThreads)
         if (lane < pb) xbuf[k0 + lane] = mine;
       }
       __syncthreads();
-      // y_j -= sum_c L[k0+c][j] x_k[c] for all j < k0: independent, coalesced rows of L
       for (int j = t; j < k0; j += kCoopThreads) {
         double lv[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++)
           lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j] : 0.0;
-        double s = xbuf[j];
+        double sacc = xbuf[j];
 #pragma unroll
-        for (int c = 0; c < kPB; c++) s -= lv[c] * yk[c];
-        xbuf[j] = s;
+        for (int c = 0; c < kPB; c++) sacc -= lv[c] * yk[c];
+        xbuf[j] = sacc;
       }
       __syncthreads();
     }

@@ -1,7 +1,7 @@
 set -x
-timeout 900 python -m pytest tests/test_front_gpu.py tests/test_matching_gpu.py -m gpu -q -x -s > gpurun_out/pytest_front.log 2>&1; echo "pytest rc=$?"
-grep -E "agreement|passed|failed" gpurun_out/pytest_front.log | tail -12
-timeout 600 python bench.py --steps 40 --warmup 5 --skip-gn > gpurun_out/bench_pad.json 2> gpurun_out/bench_pad.err; echo "bench rc=$?"
-tail -3 gpurun_out/bench_pad.err
+timeout 1200 python -m pytest tests/test_gn_gpu.py -m gpu -q -x > gpurun_out/pytest_gn.log 2>&1; echo "pytest rc=$?"
+tail -3 gpurun_out/pytest_gn.log
+timeout 300 python tools/kbench.py coop > gpurun_out/coop.log 2>&1; echo "rc=$?"; tail -14 gpurun_out/coop.log
+timeout 600 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_gn.json 2> gpurun_out/bench_gn.err; echo "bench rc=$?"
 python -c "
-import json; d=json.load(open('gpurun_out/bench_pad.json')); print(d['front_end']); print(d['frame_pipeline']); print(d['e2e'])"
+import json; d=json.load(open('gpurun_out/bench_gn.json')); g=d['gn']; print({k:g[k] for k in ('value','ms_per_iter','linearize_ms','solve_ms','begin_ms','single_call_ms_per_iter')}, g['roofline']['whole_iter_frac'])"
