@@ -217,6 +217,9 @@ __global__ void __launch_bounds__(kCoopThreads)
       if (blockIdx.x == 0 && t == 0) aprof_t = clock64();
       const int row0 = k0 + pb + rc * kTrsmRows;
       const int nrows = max(0, min(kTrsmRows, D - row0));
+      // named barrier 1 ("L11 ready"): warp 0 arrives; the TRSM warps, the y_k warp and, on the
+      // CTA that keeps the diagonal blocks for the backward phase, the inverse warp wait
+      const int bar1 = (rc == 0) ? 224 : 192;
       // 1. every operand of the panel step in one round of coalesced loads
 #pragma unroll
       for (int x = t; x < kPB * kPB; x += kCoopThreads) {
@@ -292,7 +295,7 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
         for (int c = 0; c < kPB; c++) S.L11[lane][c] = (c <= lane) ? a[c] : 0.0;
         __syncwarp();
-        asm volatile("bar.arrive 1, 192;");  // L11, dinv ready: TRSM warps and the y_k warp go
+        asm volatile("bar.arrive 1, %0;" ::"r"(bar1));  // L11, dinv ready
         COOP_ATICK(10);
       } else if (trsm_warp) {
         // 4. this thread's row: fold in the previous panel's update while warp 0 factors
@@ -313,7 +316,7 @@ __global__ void __launch_bounds__(kCoopThreads)
             }
           }
         }
-        asm volatile("bar.sync 1, 192;");
+        asm volatile("bar.sync 1, %0;" ::"r"(bar1));
         // right-looking TRSM: independent updates per column -> ILP
 #pragma unroll
         for (int c = 0; c < kPB; c++) {
@@ -337,7 +340,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         }
       } else if (warp == 5) {
         // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp
-        asm volatile("bar.sync 1, 192;");
+        asm volatile("bar.sync 1, %0;" ::"r"(bar1));
         double a[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++) a[c] = S.L11[lane][c];
@@ -351,13 +354,28 @@ __global__ void __launch_bounds__(kCoopThreads)
         __syncwarp();
         if (lane >= pb) yk[lane] = 0.0;
         asm volatile("bar.sync 2, 160;");
-        if (rc == 0) {
-          if (lane < pb) xbuf[k0 + lane] = mine;
-          double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
+        if (rc == 0 && lane < pb) xbuf[k0 + lane] = mine;
+      } else if (warp == 4 && rc == 0) {
+        // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot
+        //    products instead of a 32-pivot chain).  Lane c builds column c of M row by row:
+        //    M[r][c] = (delta_rc - sum_{k<r} L11[r][k] M[k][c]) / L11[r][r].  Runs beside the
+        //    TRSM of this panel, off the critical path.
+        asm volatile("bar.sync 1, %0;" ::"r"(bar1));
+        double mcol[kPB];
 #pragma unroll
-          for (int c = 0; c < kPB; c++) Ld[lane * kPB + c] = a[c];
-          Ld[kPB * kPB + lane] = S.dinv[lane];
+        for (int r = 0; r < kPB; r++) {
+          double s0 = (r == lane) ? 1.0 : 0.0, s1 = 0.0;
+#pragma unroll
+          for (int k = 0; k < r; k++) {
+            if (k & 1) s1 -= S.L11[r][k] * mcol[k];
+            else s0 -= S.L11[r][k] * mcol[k];
+          }
+          mcol[r] = (s0 + s1) * S.dinv[r];
         }
+        double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
+#pragma unroll
+        for (int r = 0; r < kPB; r++) Ld[r * kPB + lane] = mcol[r];
+        Ld[kPB * kPB + lane] = S.dinv[lane];
       }
       __syncthreads();
       COOP_ATICK(13);
@@ -420,30 +438,37 @@ __global__ void __launch_bounds__(kCoopThreads)
       const int pb = min(kPB, D - k0);
       double lv[kPB];
       const int j0 = t - 32;
-      if (warp == 0) {  // x_k = L11^-T y_k
-        const double *Ld = ldb + buf * kLdBuf;
-        double col[kPB];  // column `lane` of L11: col[r] = L11[r][lane]
+      if (warp == 0) {  // x_k = M^T y_k, M = L11^-1 (row-major in the buffer): one dot product per lane
+        const double *Md = ldb + buf * kLdBuf;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
 #pragma unroll
-        for (int r = 0; r < kPB; r++) col[r] = Ld[r * kPB + lane];
-        const double my_dinv = Ld[kPB * kPB + lane];
-        double mine = (lane < pb) ? xs[k0 + lane] : 0.0;
-#pragma unroll
-        for (int cc = kPB - 1; cc >= 0; cc--) {  // x_cc travels through shared memory
-          if (lane == cc) mine *= my_dinv, yk[cc] = mine;
-          __syncwarp();
-          if (lane < cc) mine -= col[cc] * yk[cc];
+        for (int r = 0; r < kPB; r += 4) {
+          s0 += Md[(r + 0) * kPB + lane] * ((r + 0 < pb) ? xs[k0 + r + 0] : 0.0);
+          s1 += Md[(r + 1) * kPB + lane] * ((r + 1 < pb) ? xs[k0 + r + 1] : 0.0);
+          s2 += Md[(r + 2) * kPB + lane] * ((r + 2 < pb) ? xs[k0 + r + 2] : 0.0);
+          s3 += Md[(r + 3) * kPB + lane] * ((r + 3 < pb) ? xs[k0 + r + 3] : 0.0);
         }
-        __syncwarp();
+        const double mine = (s0 + s1) + (s2 + s3);
+        __syncwarp();  // every lane has read y_k before it is overwritten by x_k
+        yk[lane] = (lane < pb) ? mine : 0.0;
         if (lane < pb) xs[k0 + lane] = mine;
       } else {
-        if (k0 > 0) {
-          const double *src = ldiag + static_cast<size_t>(k0 / kPB - 1) * kLdStride;
-          for (int x = j0; x < kLdBuf; x += kUpd) ldb[(buf ^ 1) * kLdBuf + x] = src[x];
-        }
+        // loads first (they only land in registers), then the prefetch that has to wait for
+        // its data before it can store to shared memory
         if (j0 < k0) {
 #pragma unroll
           for (int c = 0; c < kPB; c++)
             lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j0] : 0.0;
+        }
+        if (k0 > 0) {
+          const double *src = ldiag + static_cast<size_t>(k0 / kPB - 1) * kLdStride;
+          double pf[(kLdBuf + kUpd - 1) / kUpd];
+#pragma unroll
+          for (int i = 0; i < (kLdBuf + kUpd - 1) / kUpd; i++)
+            pf[i] = (j0 + i * kUpd < kLdBuf) ? src[j0 + i * kUpd] : 0.0;
+#pragma unroll
+          for (int i = 0; i < (kLdBuf + kUpd - 1) / kUpd; i++)
+            if (j0 + i * kUpd < kLdBuf) ldb[(buf ^ 1) * kLdBuf + j0 + i * kUpd] = pf[i];
         }
       }
       __syncthreads();
@@ -469,21 +494,14 @@ __global__ void __launch_bounds__(kCoopThreads)
     const int last = ((D - 1) / kPB) * kPB;
     for (int k0 = last; k0 >= 0; k0 -= kPB) {
       const int pb = min(kPB, D - k0);
-      if (warp == 0) {  // x_k = L11^-T y_k
-        const double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
-        double col[kPB];  // column `lane` of L11: col[r] = L11[r][lane]
-#pragma unroll
-        for (int r = 0; r < kPB; r++) col[r] = Ld[r * kPB + lane];
-        const double my_dinv = Ld[kPB * kPB + lane];
-        double mine = (lane < pb) ? xbuf[k0 + lane] : 0.0;
-#pragma unroll
-        for (int cc = kPB - 1; cc >= 0; cc--) {  // x_cc travels through shared memory
-          if (lane == cc) mine *= my_dinv, yk[cc] = mine;
-          __syncwarp();
-          if (lane < cc) mine -= col[cc] * yk[cc];
-        }
+      if (warp == 0) {  // x_k = M^T y_k
+        const double *Md = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
+        double acc = 0.0;
+#pragma unroll 8
+        for (int r = 0; r < kPB; r++) acc += Md[r * kPB + lane] * ((r < pb) ? xbuf[k0 + r] : 0.0);
         __syncwarp();
-        if (lane < pb) xbuf[k0 + lane] = mine;
+        yk[lane] = (lane < pb) ? acc : 0.0;
+        if (lane < pb) xbuf[k0 + lane] = acc;
       }
       __syncthreads();
       for (int j = t; j < k0; j += kCoopThreads) {
