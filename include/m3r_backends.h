@@ -373,6 +373,10 @@ int m3r_gn_comm_signal(m3r_gn_comm *comm, m3r_gn_workspace *ws, void *stream);
  * the summed system, i.e. everything m3r_gn_solve_retract reads. */
 int m3r_gn_comm_reduce(m3r_gn_comm *comm, m3r_gn_workspace *ws, double *out, int num_poses,
                        void *stream);
+/* Exchange algorithm of m3r_gn_comm_reduce: 0 = chosen by size (one-shot below 8 MB or fewer
+ * than 4 ranks, else reduce-scatter + all-gather), 1 = always one-shot, 2 = always two-phase.
+ * Process-wide; for tests and benchmarks. */
+void m3r_debug_set_exchange_mode(int mode);
 
 #ifdef __cplusplus
 }

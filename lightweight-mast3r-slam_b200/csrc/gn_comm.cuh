@@ -6,6 +6,13 @@
 // order, so all ranks obtain bitwise identical sums and the replicated Cholesky solves stay in
 // lockstep.  One arrival flag per (reader, writer) pair carries the round number; buffers are
 // double-buffered by round parity, which makes a second barrier unnecessary (header comment).
+//
+// Large systems (256 keyframes: 25.5 MB) on 4+ ranks use a two-phase variant instead, because
+// the one-shot form makes every rank pull W-1 whole buffers (89 MB inbound at 8 ranks, 0.22 ms):
+// reduce-scatter -- rank p sums rows [b_p, b_p+1) of all buffers in rank order into its `red`
+// buffer -- then all-gather -- every rank copies each peer's reduced slice.  Inbound traffic per
+// rank drops to 2 (W-1)/W of ONE buffer; every element is still summed by exactly one rank in
+// rank order, so the replicas stay bitwise identical.
 #pragma once
 
 namespace m3r {
@@ -35,17 +42,88 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double *p) {
 struct CommTable {
   int *flags[kCommMaxWorld];            // flags[p]: flag block of rank p (peer-mapped)
   const double *buf[2][kCommMaxWorld];  // buf[parity][p]: system buffer of rank p
+  double *red[2][kCommMaxWorld];        // red[parity][p]: reduced slice of rank p (two-phase)
+};
+
+struct CommSlices {
+  int begin[kCommMaxWorld + 1];  // rank p reduces rows [begin[p], begin[p+1]) of the D+1 rows
 };
 
 // "my buffer of round `round` is complete": one release store per peer.  The buffer was written
 // by earlier kernels on this stream (visible at the device's L2, which is where peer reads land).
 __global__ void comm_signal_kernel(const CommTable T, int rank, int world, int round,
-                                   const int *__restrict__ stop) {
+                                   const int *__restrict__ stop, int flag_set) {
   if (stop[0]) return;
   const int p = threadIdx.x;
   if (p < world) {
     __threadfence_system();
-    st_release_sys(T.flags[p] + rank, round);
+    st_release_sys(T.flags[p] + flag_set * kCommMaxWorld + rank, round);
+  }
+}
+
+// true when every rank's flag of `flag_set` has reached `round` (false: timed out)
+__device__ __forceinline__ bool comm_wait_all(const CommTable &T, int rank, int world, int round,
+                                              int flag_set, int *timed_out) {
+  if (threadIdx.x == 0) *timed_out = 0;
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const int *f = T.flags[rank] + flag_set * kCommMaxWorld + threadIdx.x;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(f) < round) {
+      if (clock64() - t0 > 8000000000LL) {  // ~4 s: a peer died; do not hang the GPU
+        *timed_out = 1;
+        break;
+      }
+      __nanosleep(100);
+    }
+  }
+  __syncthreads();
+  return *timed_out == 0;
+}
+
+__device__ __forceinline__ int comm_row_len(int r, int D) { return (r < D) ? 7 * (r / 7 + 1) : D; }
+
+// two-phase, phase 1: reduce this rank's rows over all ranks' buffers into red[par][rank]
+__global__ void __launch_bounds__(256)
+    comm_reduce_scatter_kernel(const CommTable T, const CommSlices S, int rank, int world, int round,
+                               int D, int *__restrict__ ws_flags) {
+  if (ws_flags[0]) return;
+  __shared__ int timed_out;
+  if (!comm_wait_all(T, rank, world, round, 0, &timed_out)) {
+    if (threadIdx.x == 0) ws_flags[3] = 1;
+    return;
+  }
+  const int par = round & 1;
+  double *dst = T.red[par][rank];
+  for (int r = S.begin[rank] + blockIdx.x; r < S.begin[rank + 1]; r += gridDim.x) {
+    const int len = comm_row_len(r, D);
+    const size_t off = static_cast<size_t>(r) * D;
+    for (int c = threadIdx.x; c < len; c += blockDim.x) {
+      double s = 0.0;
+      for (int p = 0; p < world; p++) s += ld_relaxed_sys_f64(T.buf[par][p] + off + c);
+      dst[off + c] = s;
+    }
+  }
+}
+
+// two-phase, phase 2: copy every rank's reduced rows
+__global__ void __launch_bounds__(256)
+    comm_gather_kernel(const CommTable T, const CommSlices S, int rank, int world, int round,
+                       double *__restrict__ out, int D, int *__restrict__ ws_flags) {
+  if (ws_flags[0]) return;
+  __shared__ int timed_out;
+  if (!comm_wait_all(T, rank, world, round, 1, &timed_out)) {
+    if (threadIdx.x == 0) ws_flags[3] = 1;
+    return;
+  }
+  const int par = round & 1;
+  for (int r = blockIdx.x; r <= D; r += gridDim.x) {
+    int p = 0;
+    while (r >= S.begin[p + 1]) p++;
+    const double *src = T.red[par][p];
+    const int len = comm_row_len(r, D);
+    const size_t off = static_cast<size_t>(r) * D;
+    for (int c = threadIdx.x; c < len; c += blockDim.x) out[off + c] = ld_relaxed_sys_f64(src + off + c);
   }
 }
 
@@ -58,21 +136,7 @@ __global__ void __launch_bounds__(256)
                        int D, int *__restrict__ ws_flags) {
   if (ws_flags[0]) return;
   __shared__ int timed_out;
-  if (threadIdx.x == 0) timed_out = 0;
-  __syncthreads();
-  if (threadIdx.x < world) {
-    const int *f = T.flags[rank] + threadIdx.x;
-    const long long t0 = clock64();
-    while (ld_acquire_sys(f) < round) {
-      if (clock64() - t0 > 8000000000LL) {  // ~4 s: a peer died; do not hang the GPU
-        timed_out = 1;
-        break;
-      }
-      __nanosleep(100);
-    }
-  }
-  __syncthreads();
-  if (timed_out) {
+  if (!comm_wait_all(T, rank, world, round, 0, &timed_out)) {
     if (threadIdx.x == 0) ws_flags[3] = 1;
     return;
   }
@@ -93,7 +157,7 @@ __global__ void __launch_bounds__(256)
 struct m3r_gn_comm {
   int device = 0, rank = 0, world = 1;
   long long cap = 0;          // doubles per system buffer (even)
-  unsigned char *area = nullptr;  // [flags | buf0 | buf1], cudaMalloc'ed here
+  unsigned char *area = nullptr;  // [flags | buf0 | buf1 | red0 | red1], cudaMalloc'ed here
   void *peer_area[m3r::kCommMaxWorld] = {nullptr};
   bool opened[m3r::kCommMaxWorld] = {false};  // mapped through cudaIpcOpenMemHandle
   bool connected = false;
@@ -101,8 +165,12 @@ struct m3r_gn_comm {
   m3r::CommTable table{};
 };
 
+static std::atomic<int> g_exchange_mode{0};  // 0 by size, 1 one-shot, 2 two-phase
+
+extern "C" void m3r_debug_set_exchange_mode(int mode) { g_exchange_mode.store(mode, std::memory_order_relaxed); }
+
 static size_t comm_area_bytes(long long cap) {
-  return static_cast<size_t>(m3r::kCommFlagBytes) + 2 * static_cast<size_t>(cap) * sizeof(double);
+  return static_cast<size_t>(m3r::kCommFlagBytes) + 4 * static_cast<size_t>(cap) * sizeof(double);
 }
 
 static void comm_fill_table(m3r_gn_comm *c) {
@@ -111,6 +179,8 @@ static void comm_fill_table(m3r_gn_comm *c) {
     c->table.flags[p] = reinterpret_cast<int *>(base);
     c->table.buf[0][p] = reinterpret_cast<const double *>(base + m3r::kCommFlagBytes);
     c->table.buf[1][p] = c->table.buf[0][p] + c->cap;
+    c->table.red[0][p] = reinterpret_cast<double *>(base + m3r::kCommFlagBytes) + 2 * c->cap;
+    c->table.red[1][p] = c->table.red[0][p] + c->cap;
   }
   c->connected = true;
 }
@@ -209,7 +279,7 @@ extern "C" int m3r_gn_comm_signal(m3r_gn_comm *c, m3r_gn_workspace *ws, void *st
   M3R_REQUIRE(c && ws, "gn_comm_signal: null pointer");
   M3R_REQUIRE(c->connected && c->round > 0, "gn_comm_signal: no round in progress");
   m3r::comm_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->table, c->rank, c->world,
-                                                                         c->round, ws->flags);
+                                                                         c->round, ws->flags, 0);
   M3R_LAUNCH_CHECK("comm_signal_kernel");
   return M3R_OK;
 }
@@ -221,9 +291,38 @@ extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *
   M3R_REQUIRE(num_poses >= 2 && m3r_gn_system_size(num_poses) <= c->cap,
               "gn_comm_reduce: system of %d poses exceeds the exchange area", num_poses);
   const int D = 7 * (num_poses - 1);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int forced = g_exchange_mode.load(std::memory_order_relaxed);  // m3r_debug_set_exchange_mode
+  const bool two_phase = forced == 2 || (forced == 0 && c->world >= 4 && m3r_gn_system_size(num_poses) >= (1 << 20));
+  if (two_phase && c->world > 1) {
+    // rows split so that every rank reduces about the same number of elements
+    m3r::CommSlices S{};
+    long long total = D;  // the right-hand-side row
+    for (int r = 0; r < D; r++) total += 7 * (r / 7 + 1);
+    long long acc = 0;
+    int p = 1;
+    S.begin[0] = 0;
+    for (int r = 0; r <= D && p < c->world; r++) {
+      acc += (r < D) ? 7 * (r / 7 + 1) : D;
+      if (acc * c->world >= total * p) S.begin[p++] = r + 1;
+    }
+    for (; p <= c->world; p++) S.begin[p] = D + 1;
+    S.begin[c->world] = D + 1;
+    const int mine = S.begin[c->rank + 1] - S.begin[c->rank];
+    const int rs_blocks = mine < m3r::kNumSMs * 4 ? (mine > 0 ? mine : 1) : m3r::kNumSMs * 4;
+    m3r::comm_reduce_scatter_kernel<<<rs_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, D,
+                                                             ws->flags);
+    M3R_LAUNCH_CHECK("comm_reduce_scatter_kernel");
+    m3r::comm_signal_kernel<<<1, 32, 0, s>>>(c->table, c->rank, c->world, c->round, ws->flags, 1);
+    M3R_LAUNCH_CHECK("comm_signal_kernel");
+    const int ag_blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
+    m3r::comm_gather_kernel<<<ag_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, out, D,
+                                                     ws->flags);
+    M3R_LAUNCH_CHECK("comm_gather_kernel");
+    return M3R_OK;
+  }
   const int blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
-  m3r::comm_reduce_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      c->table, c->rank, c->world, c->round, out, D, ws->flags);
+  m3r::comm_reduce_kernel<<<blocks, 256, 0, s>>>(c->table, c->rank, c->world, c->round, out, D, ws->flags);
   M3R_LAUNCH_CHECK("comm_reduce_kernel");
   return M3R_OK;
 }

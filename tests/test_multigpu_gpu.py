@@ -29,12 +29,14 @@ def _stage(kind, g, dev, rank, world):
     return st, Twc
 
 
+@pytest.mark.parametrize("mode", [1, 2], ids=["oneshot", "twophase"])
 @pytest.mark.parametrize("kind", KINDS)
-def test_peer_exchange_two_gpus(backends, kind):
+def test_peer_exchange_two_gpus(backends, kind, mode):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     from mast3r_slam_backends import _lib
 
+    _lib.debug_set_exchange_mode(mode)  # reduce in one shot / reduce-scatter + all-gather
     world, iters = 2, 4
     g = synth.make_graph(7, 96, 128, seed=5)
     devs = [torch.device("cuda", r) for r in range(world)]
@@ -81,3 +83,4 @@ def test_peer_exchange_two_gpus(backends, kind):
     assert err < 1e-5
     for c in comms:
         _lib.gn_comm_destroy(c)
+    _lib.debug_set_exchange_mode(0)
