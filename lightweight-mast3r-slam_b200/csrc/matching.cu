@@ -365,10 +365,19 @@ __global__ void __launch_bounds__(kMcThreads)
       valid_opt[row + k] = vo ? 1 : 0;
       c_opt += vo;
     }
-    if (bitmap && vm && inb) {
-      const unsigned bit = 1u << (j & 31);
-      const unsigned old = atomicOr(bitmap + static_cast<size_t>(b) * bitmap_words + (j >> 5), bit);
-      c_uni += (old & bit) == 0;
+    // distinct-index count: lanes of a warp that hit the same bitmap word (the common case: a
+    // smooth match field maps 32 neighbouring points into one or two words) merge their bits
+    // and issue ONE atomicOr; the bits that were clear before are the first occurrences
+    const bool mark = bitmap && vm && inb;
+    const unsigned marking = __ballot_sync(__activemask(), mark);
+    if (mark) {
+      const int word = static_cast<int>(j >> 5);
+      const unsigned peers = __match_any_sync(marking, word);
+      const unsigned bits = __reduce_or_sync(peers, 1u << (j & 31));
+      if ((threadIdx.x & 31) == __ffs(peers) - 1) {
+        const unsigned old = atomicOr(bitmap + static_cast<size_t>(b) * bitmap_words + word, bits);
+        c_uni += __popc(bits & ~old);
+      }
     }
   }
   __shared__ int red[3][kMcThreads / 32];
