@@ -27,7 +27,6 @@ namespace m3r {
 constexpr int kTrThreads = 512;
 constexpr int kTrWarps = kTrThreads / 32;
 constexpr int kTrAcc = 36;        // 28 (upper triangle of H) + 7 (J^T W r) + 1 (cost)
-constexpr int kTrCap = 6144;      // staged points per CTA (8 floats each = 192 KB)
 
 struct TrackArgs {
   const float *Xf;            // [n_f,3] frame pointmap (gathered through idx when non-null)
@@ -57,6 +56,10 @@ struct TrackSmem {
   int stop;    // 0 continue, 1 converged, 2 factorisation failed
   double cost;
 };
+constexpr int kTrSmemMax = 227 * 1024;
+constexpr int kTrRecBase = (static_cast<int>(sizeof(TrackSmem)) + 15) & ~15;
+// staged points per CTA: 8 floats each in what the fixed part leaves of the 227 KB
+constexpr int kTrCap = ((kTrSmemMax - kTrRecBase) / 32) & ~31;
 
 // 7x7 SPD solve H x = g in fp64 (H given by its upper triangle, row-major packed).  Fully
 // unrolled: the factor lives in registers, one rsqrt per pivot and no divisions.  Returns
@@ -250,7 +253,7 @@ template <int KIND, bool STAGED>
 __global__ void __launch_bounds__(kTrThreads, 1) track_pose_kernel(const TrackArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TrackSmem &S = *reinterpret_cast<TrackSmem *>(smem_raw);
-  float *rec = reinterpret_cast<float *>(smem_raw + ((sizeof(TrackSmem) + 15) & ~size_t(15)));
+  float *rec = reinterpret_cast<float *>(smem_raw + kTrRecBase);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = gridDim.x;
   const int chunk = (A.n + G - 1) / G;
@@ -391,7 +394,7 @@ static int launch_track(const TrackArgs &A, int grid, size_t smem, cudaStream_t 
   bool &attr_set = attr_set_dev[dev & 63];
   if (!attr_set) {
     M3R_CUDA_TRY(cudaFuncSetAttribute(track_pose_kernel<KIND, STAGED>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, kTrSmemMax));
     attr_set = true;
   }
   TrackArgs args = A;
@@ -442,8 +445,7 @@ extern "C" int m3r_track_pose(const m3r_track_params *prm, const float *Xf, int6
   if (grid > kNumSMs) grid = kNumSMs;
   const int chunk = static_cast<int>((n + grid - 1) / grid);
   const bool staged = chunk <= kTrCap;
-  const size_t base = (sizeof(TrackSmem) + 15) & ~size_t(15);
-  const size_t smem = base + (staged ? static_cast<size_t>(chunk) * 8 * sizeof(float) : 0);
+  const size_t smem = static_cast<size_t>(kTrRecBase) + (staged ? static_cast<size_t>(chunk) * 8 * sizeof(float) : 0);
   if (prm->kind == M3R_GN_RAYS)
     return staged ? launch_track<M3R_GN_RAYS, true>(A, grid, smem, s)
                   : launch_track<M3R_GN_RAYS, false>(A, grid, smem, s);

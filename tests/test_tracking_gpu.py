@@ -137,6 +137,23 @@ def test_unstaged_path_large_n(tracking, oracle):
     assert _rel(Tw, To) < TOL and _rel(Tk, Tko) < TOL
 
 
+@pytest.mark.parametrize("n_target", [148 * 5500, 148 * 5700, 148 * 6200])
+def test_staging_capacity_boundary(tracking, oracle, n_target):
+    """Point counts just below and above what the shared-memory staging holds (about 5.6k points
+    per CTA next to the 47 KB of reduction buffers): both sides must launch and agree."""
+    cfg = dict(synth.TRACK_DEFAULTS, rel_error=0.0, delta_norm=0.0, max_iters=2)
+    tracking.set_config({"tracking": cfg})
+    t = synth.make_track_inputs(96, 128, seed=12)
+    rep = -(-n_target // t["n"])
+    d = _cuda({k: (t[k].repeat(rep, 1)[:n_target].contiguous() if k in ("Xf", "Xk", "Qk", "valid_opt") else t[k])
+               for k in t})
+    Tw, Tk = tracking.opt_pose_ray_dist_sim3(d["Xf"], d["Xk"], d["T_WCf_init"], d["T_WCk"], d["Qk"], d["valid_opt"])
+    assert tracking.last_info.status == 0 and tracking.last_info.iterations == 2
+    c = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in d.items()}
+    To, Tko, _, _ = oracle.track_pose_rays(c["Xf"], c["Xk"], c["T_WCf_init"], c["T_WCk"], c["Qk"], c["valid_opt"], cfg)
+    assert _rel(Tw, To) < TOL and _rel(Tk, Tko) < TOL
+
+
 def test_degenerate_and_errors(tracking):
     tracking.set_config({"tracking": dict(synth.TRACK_DEFAULTS)})
     d = _cuda(synth.make_track_inputs(24, 32, seed=11))
