@@ -427,6 +427,21 @@ def time_tracking(steps, warmup, cpu=True):
         out[kind] = {"ms_per_call": ms, "iterations": iters, "us_per_iter": (ms45 - ms5) / 40 * 1e3,
                      "fixed_us": (ms5 - 5 * (ms45 - ms5) / 40) * 1e3, "gpu_launches_per_call": 1}
     tr.set_config({"tracking": base})
+    # what the reference itself runs on a GPU: its torch loop (tracker.py:173-215) op for op,
+    # two host syncs per iteration (synth.torch_track_pose_rays)
+    for _ in range(2):
+        synth.torch_track_pose_rays(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"], t["valid_opt"])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        Tw_t, _, it_t = synth.torch_track_pose_rays(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"],
+                                                    t["valid_opt"])
+    torch.cuda.synchronize()
+    out["torch_gpu_rays_ms_per_call"] = (time.perf_counter() - t0) / reps * 1e3
+    out["torch_gpu_iterations"] = it_t
+    Tw_k, _ = tr.opt_pose_ray_dist_sim3(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"], t["valid_opt"])
+    out["kernel_vs_torch_gpu_pose_max_abs_diff"] = float((Tw_k - Tw_t).abs().max())
     if cpu:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import m3r_oracle as oracle

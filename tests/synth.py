@@ -308,3 +308,100 @@ def make_track_inputs(h, w, seed=0, device="cpu", pose_noise=0.03, point_noise=2
                 T_WCf_init=g["Twc_init"][1:2].contiguous(), T_WCf_true=g["Twc_true"][1:2].contiguous(),
                 K=g["K"], h=h, w=w, n=n, Xf=Xf_canon[idx].contiguous(), Qk=Qk.contiguous(), Cf=Cf.contiguous(),
                 valid_opt=valid_opt.contiguous(), meas_k=meas.contiguous(), valid_meas_k=valid_meas.contiguous())
+
+
+# ------------------------------------------------------------------------------------------
+# the reference's tracking loop as plain torch on any device (timing baseline for bench.py:
+# what FrameTracker.opt_pose_ray_dist_sim3 executes on the GPU -- ~40 torch kernels and two
+# host syncs per iteration -- with lietorch's Sim3 replaced by the torch ops below)
+# ------------------------------------------------------------------------------------------
+def sim3_exp(xi):
+    """Exp of (tau, omega, sigma) [...,7] -> Sim3 data [...,8] (lietorch rxso3/sim3 formulas,
+    general branch with guards; gn_kernels.cu:323-390)."""
+    tau, phi, sigma = xi[..., :3], xi[..., 3:6], xi[..., 6:7]
+    scale = torch.exp(sigma)
+    th2 = (phi * phi).sum(-1, keepdim=True)
+    th = torch.sqrt(th2)
+    small_t, small_s = th < 1e-6, sigma.abs() < 1e-6
+    th_s = torch.where(small_t, torch.ones_like(th), th)
+    th2_s = th_s * th_s
+    sg_s = torch.where(small_s, torch.ones_like(sigma), sigma)
+    q = torch.cat([phi * torch.where(small_t, 0.5 - th2 / 48, torch.sin(0.5 * th_s) / th_s),
+                   torch.where(small_t, 1 - th2 / 8, torch.cos(0.5 * th_s))], dim=-1)
+    C = torch.where(small_s, torch.ones_like(sigma), (scale - 1) / sg_s)
+    a, b, c = scale * torch.sin(th_s), scale * torch.cos(th_s), th2_s + sg_s * sg_s
+    A_gen = (a * sg_s + (1 - b) * th_s) / (th_s * c)
+    B_gen = (C - ((b - 1) * sg_s + a * th_s) / c) / th2_s
+    A_s0 = (1 - torch.cos(th_s)) / th2_s
+    B_s0 = (th_s - torch.sin(th_s)) / (th2_s * th_s)
+    A_t0 = ((sg_s - 1) * scale + 1) / (sg_s * sg_s)
+    B_t0 = (scale * 0.5 * sg_s * sg_s + scale - 1 - sg_s * scale) / (sg_s * sg_s * sg_s)
+    A = torch.where(small_s, torch.where(small_t, torch.full_like(th, 0.5), A_s0),
+                    torch.where(small_t, A_t0, A_gen))
+    B = torch.where(small_s, torch.where(small_t, torch.full_like(th, 1 / 6), B_s0),
+                    torch.where(small_t, B_t0, B_gen))
+    pt = torch.linalg.cross(phi, tau)
+    t = C * tau + A * pt + B * torch.linalg.cross(phi, pt)
+    return torch.cat([t, q, scale], dim=-1)
+
+
+def sim3_mul(A, B):
+    """A * B on Sim3 data [...,8]."""
+    t = A[..., 7:8] * (quat_to_R(A[..., 3:7]) @ B[..., :3].unsqueeze(-1)).squeeze(-1) + A[..., :3]
+    return torch.cat([t, quat_mul(A[..., 3:7], B[..., 3:7]), A[..., 7:8] * B[..., 7:8]], dim=-1)
+
+
+def sim3_inv(A):
+    qi = A[..., 3:7] * torch.tensor([-1.0, -1.0, -1.0, 1.0], device=A.device)
+    si = 1.0 / A[..., 7:8]
+    t = -si * (quat_to_R(qi) @ A[..., :3].unsqueeze(-1)).squeeze(-1)
+    return torch.cat([t, qi, si], dim=-1)
+
+
+def torch_track_pose_rays(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=None):
+    """tracker.py:157-215 op for op in torch, on the tensors' device; returns (T_WCf, T_CkCf,
+    iterations)."""
+    import math
+
+    c = dict(TRACK_DEFAULTS, **(cfg or {}))
+    dev = Xf.device
+    si_ray = 1 / c["sigma_ray"] * valid * torch.sqrt(Qk)
+    si_dist = 1 / c["sigma_dist"] * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((si_ray.repeat(1, 3), si_dist), dim=1)
+    T = sim3_mul(sim3_inv(T_WCk), T_WCf)
+    d = torch.linalg.norm(Xk, dim=-1, keepdim=True)
+    rd_k = torch.cat(((1.0 / d) * Xk, d), dim=-1)
+    old_cost, it = float("inf"), 0
+    for step in range(c["max_iters"]):
+        pW = sim3_act(T, Xf.unsqueeze(0)).squeeze(0)
+        x, y, z = pW.unbind(-1)
+        o = torch.zeros_like(x)
+        skew = torch.stack([o, -z, y, z, o, -x, -y, x, o], dim=-1).view(-1, 3, 3)
+        dP = torch.cat([torch.eye(3, device=dev).repeat(pW.shape[0], 1, 1), -skew, pW.unsqueeze(-1)], dim=-1)
+        dd = torch.linalg.norm(pW, dim=-1, keepdim=True)
+        d_inv = 1.0 / dd
+        r_ = d_inv * pW
+        rd_f = torch.cat((r_, dd), dim=-1)
+        eye = torch.eye(3, device=dev).repeat(pW.shape[0], 1, 1)
+        dr = d_inv.unsqueeze(-1) * (eye - (d_inv ** 2).unsqueeze(-1) * (pW.unsqueeze(-1) @ pW.unsqueeze(-2)))
+        drd = torch.cat((dr, r_.unsqueeze(-2)), dim=-2)
+        r = rd_k - rd_f
+        J = -drd @ dP
+        wr = sqrt_info * r
+        r_abs = torch.abs(wr)
+        hub = torch.where(r_abs < c["huber"], torch.ones(1, device=dev), c["huber"] / r_abs)
+        rsi = sqrt_info * torch.sqrt(hub)
+        A = (rsi[..., None] * J).view(-1, 7)
+        b = (rsi * r).view(-1, 1)
+        H = A.T @ A
+        g = -A.T @ b
+        cost = 0.5 * (b.T @ b).item()
+        L = torch.linalg.cholesky(H, upper=False)
+        tau = torch.cholesky_solve(g, L, upper=False).view(1, -1)
+        T = sim3_mul(sim3_exp(tau), T)
+        it = step + 1
+        rel_dec = math.fabs((old_cost - cost) / old_cost) if old_cost != 0 else float("nan")
+        if rel_dec < c["rel_error"] or torch.linalg.norm(tau) < c["delta_norm"]:
+            break
+        old_cost = cost
+    return sim3_mul(T_WCk, T), T, it
