@@ -597,14 +597,32 @@ __global__ void __launch_bounds__(64)
     if (t == 0) nhit = __popc(lo) + __popc(hi);
     __syncthreads();
     const int nh = nhit;
-    for (int k = 0; k < nh; k++) {
-      const int hle = hit[k] >> 2, hc = hit[k] & 3;
-      if (t < 49) {
-        const double v = edge_H[static_cast<size_t>(hle) * 49 + t];
-        accH += (hc == 3) ? -v : v;
-      } else if (t < 56 && a == b) {
-        const double g = edge_g[static_cast<size_t>(hle) * 7 + (t - 49)];
-        accg += (hc == 1) ? -g : g;  // g_i = -g_j
+    // eight hits per round: the loads of a round are independent and issued together (a
+    // diagonal block of a well connected keyframe collects dozens of edges; one L2 round trip
+    // per edge was the whole cost of this kernel), the adds keep the edge order
+    constexpr int kHitUnroll = 8;
+    for (int k0 = 0; k0 < nh; k0 += kHitUnroll) {
+      double v[kHitUnroll];
+#pragma unroll
+      for (int u = 0; u < kHitUnroll; u++) {
+        v[u] = 0.0;
+        if (k0 + u < nh) {
+          const int hle = hit[k0 + u] >> 2, hc = hit[k0 + u] & 3;
+          if (t < 49) {
+            const double x = edge_H[static_cast<size_t>(hle) * 49 + t];
+            v[u] = (hc == 3) ? -x : x;
+          } else if (t < 56 && a == b) {
+            const double g = edge_g[static_cast<size_t>(hle) * 7 + (t - 49)];
+            v[u] = (hc == 1) ? -g : g;  // g_i = -g_j
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kHitUnroll; u++) {
+        if (k0 + u < nh) {
+          if (t < 49) accH += v[u];
+          else accg += v[u];
+        }
       }
     }
     __syncthreads();
