@@ -1,1 +1,1 @@
-timeout 300 ncu --set full --import-source on --clock-control none --profile-from-start off -k regex:"gn_assemble" -c 2 -o gpurun_out/asm_full -f python tools/run_gn_once.py > gpurun_out/ncu_asm.log 2>&1; echo "ncu rc=$?"
+timeout 600 python -m pytest tests/test_streams_gpu.py -m gpu -q -x 2>&1 | tail -15
