@@ -730,7 +730,12 @@ def main():
                              "both 62 us per frame at 1965 MHz, not by HBM",
                      "half_op_per_s": 2 * half_macs / (r["refine_ms"] * 1e-3),
                      "fp16_pipe_frac": (2 * half_macs / 2 / 32) / (148 * 4 * 0.486 * 1.965e9) /
-                                       (r["refine_ms"] * 1e-3)},
+                                       (r["refine_ms"] * 1e-3),
+                     # 245 windows x 3 LDS.128 per point, 4 wavefronts per warp-wide LDS.128 when
+                     # conflict-free, one wavefront per clock per SM; the ncu capture shows 1.44x
+                     # this many wavefronts (bank-conflict replays of a noisy gather)
+                     "smem_pipe_frac_conflict_free": (N_PTS / 32 * 245 * 3 * 4) / (148 * 1.965e9) /
+                                                     (r["refine_ms"] * 1e-3)},
         "kernels": {"iter_proj_ms": r["iter_proj_ms"], "cast_ms": r["cast_ms"], "refine_ms": r["refine_ms"],
                     "iter_proj_gbs": iproj_gbs, "iter_proj_frac": iproj_gbs / peak,
                     "pair_gbs": pair_gbs, "pair_frac": pair_gbs / peak},
