@@ -220,7 +220,9 @@ __global__ void __launch_bounds__(kCoopThreads)
       // named barrier 1 ("L11 ready"): warp 0 arrives; the TRSM warps, the y_k warp and, on the
       // CTA that keeps the diagonal blocks for the backward phase, the inverse warp wait
       const int bar1 = (rc == 0) ? 224 : 192;
-      // 1. every operand of the panel step in one round of coalesced loads
+      // 1. what the POTRF needs (diagonal block, the previous panel's rows of it, rhs) by all
+      //    threads; the CTA's 128 panel rows are loaded by the TRSM warps themselves AFTER this
+      //    barrier, beside the diagonal-block update and the POTRF instead of in front of them
 #pragma unroll
       for (int x = t; x < kPB * kPB; x += kCoopThreads) {
         const int r = x / kPB, c = x % kPB;
@@ -230,61 +232,64 @@ __global__ void __launch_bounds__(kCoopThreads)
         S.Ad[r][c] = v;
         S.Ls[r][c] = (la && r < pb) ? A[g + kp + c] : 0.0;
       }
-#pragma unroll
-      for (int x = t; x < kTrsmRows * kPB; x += kCoopThreads) {
-        const int r = x / kPB, c = x % kPB;
-        const size_t g = static_cast<size_t>(row0 + r) * D;
-        S.u.a.Xr[r][c] = (r < nrows && c < pb) ? A[g + k0 + c] : 0.0;
-        S.u.a.Lp[r][c] = (la && r < nrows) ? A[g + kp + c] : 0.0;
-      }
       if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
       __syncthreads();
       COOP_ATICK(8);
+      if (trsm_warp) {
+        const int tt = trsm_slot * 32 + lane;
+#pragma unroll 8
+        for (int x = tt; x < kTrsmRows * kPB; x += 128) {
+          const int r = x / kPB, c = x % kPB;
+          const size_t g = static_cast<size_t>(row0 + r) * D;
+          S.u.a.Xr[r][c] = (r < nrows && c < pb) ? A[g + k0 + c] : 0.0;
+          S.u.a.Lp[r][c] = (la && r < nrows) ? A[g + kp + c] : 0.0;
+        }
+        asm volatile("bar.sync 4, 128;");  // the four TRSM warps: rows staged
+      }
       // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
       //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
       //    272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner
       //    dimension; the halves meet in shared memory.  Entries above the diagonal receive
       //    garbage and are never read.  (The first version gave every thread 4 outputs of one
       //    row: 5 shared loads per 4 DFMA, 4.2 us per panel on the critical path.)
-      if (la) {
+      if (la && !trsm_warp) {
         double acc[4][4];
-        const int tile = t & 63, half = t >> 6;
+        const int u = ((warp == 0) ? 0 : (warp == 4) ? 1 : (warp == 5) ? 2 : 3) * 32 + lane;
+        const int tile = u & 63, half = u >> 6;
         const int tr = tile >> 3, tc = tile & 7;
-        if (t < 128) {
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int k = 0; k < 4; k++) acc[i][k] = 0.0;
+#pragma unroll 4
+        for (int j = half * (kPB / 2); j < (half + 1) * (kPB / 2); j += 2) {
+          double2 av[4], bv[4];
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            av[i] = *reinterpret_cast<const double2 *>(&S.Ls[tr + 8 * i][j]);
+            bv[i] = *reinterpret_cast<const double2 *>(&S.Ls[tc + 8 * i][j]);
+          }
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int k = 0; k < 4; k++) acc[i][k] = 0.0;
-#pragma unroll 4
-          for (int j = half * (kPB / 2); j < (half + 1) * (kPB / 2); j += 2) {
-            double2 av[4], bv[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-              av[i] = *reinterpret_cast<const double2 *>(&S.Ls[tr + 8 * i][j]);
-              bv[i] = *reinterpret_cast<const double2 *>(&S.Ls[tc + 8 * i][j]);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; i++)
-#pragma unroll
-              for (int k = 0; k < 4; k++) acc[i][k] += av[i].x * bv[k].x + av[i].y * bv[k].y;
-          }
+            for (int k = 0; k < 4; k++) acc[i][k] += av[i].x * bv[k].x + av[i].y * bv[k].y;
         }
-        if (t >= 64 && t < 128) {
+        if (half == 1) {
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
             for (int k = 0; k < 4; k++) S.dpart[(i * 4 + k) * 64 + tile] = acc[i][k];
         }
-        __syncthreads();
-        if (t < 64) {
+        asm volatile("bar.sync 3, 128;");  // warps 0, 4, 5, 7
+        if (half == 0) {
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
             for (int k = 0; k < 4; k++)
               S.Ad[tr + 8 * i][tc + 8 * k] -= acc[i][k] + S.dpart[(i * 4 + k) * 64 + tile];
         }
+        asm volatile("bar.sync 3, 128;");  // the updated diagonal block is complete
       }
-      __syncthreads();
       COOP_ATICK(9);
       if (warp == 0) {
         // 3. POTRF (rows in registers, shuffles)
