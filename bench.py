@@ -365,6 +365,28 @@ def time_frame_pipeline(sets, M, steps, warmup):
         pointmaps.update_pointmap(Xk_canon, Ck_sum, Xkf, Ckf, "weighted_pointmap", T=T_CkCf)
         return counts
 
+    def torch_epilogues(idx, valid):
+        """tracker.py:41,59-67,104-110 and frame.py:74-77 as the reference issues them (torch)."""
+        i1 = idx[0]
+        Qk = torch.sqrt(t["Qff"][i1] * t["Qkf"])
+        vm = valid[0]
+        valid_opt = vm & (t["Cf_canon"][i1] > T["C_conf"]) & (t["Ck"] > T["C_conf"]) & (Qk > T["Q_conf"])
+        valid_kf = vm & (Qk > T["Q_conf"])
+        fr = (valid_opt.sum() / valid_opt.numel(), valid_kf.sum() / valid_kf.numel())
+        uniq = torch.unique(i1[vm[:, 0]]).shape[0]  # host sync, as in the reference
+        Xn = ((Ck_sum * Xk_canon) + (Ckf * Xkf)) / (Ck_sum + Ckf)
+        return fr, uniq, Xn, Ck_sum + Ckf
+
+    idx_w, valid_w = front.match(*FRONT_INPUTS[0], sets[0]["D11"], sets[0]["D21"])
+    for _ in range(3):
+        torch_epilogues(idx_w, valid_w)
+    torch.cuda.synchronize()
+    tt0 = time.perf_counter()
+    for _ in range(10):
+        torch_epilogues(idx_w, valid_w)
+    torch.cuda.synchronize()
+    torch_epi_ms = (time.perf_counter() - tt0) / 10 * 1e3
+
     for i in range(warmup):
         frame(i)
     torch.cuda.synchronize()
@@ -377,7 +399,11 @@ def time_frame_pipeline(sets, M, steps, warmup):
     torch.cuda.synchronize()
     ms = t0.elapsed_time(t1) / steps
     return {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "gpu_launches_per_frame": (_lib.launch_count() - l0) / steps,
-            "stages": "match(3) + match_confidence(1) + track_pose(1) + update_pointmap(1); memsets not counted"}
+            "stages": "match(3) + match_confidence(1) + track_pose(1) + update_pointmap(1); memsets not counted",
+            "torch_confidence_and_update_ms": torch_epi_ms,
+            "torch_note": "the reference's torch lines for the confidence/fraction/unique epilogue and the weighted "
+                          "keyframe update alone (wall clock, includes torch.unique's host sync); here they are two "
+                          "of the six launches"}
 
 
 def time_tracking(steps, warmup, cpu=True):
