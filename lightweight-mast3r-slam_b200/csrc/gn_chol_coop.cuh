@@ -33,6 +33,17 @@ __device__ long long g_coop_prof[16];  // [8..13]: phase A split of CTA 0, see C
 
 // phase A of CTA 0, thread 0 (warp 0): [8] stage previous L21, [9] loads + look-ahead update,
 // [10] POTRF, [11] y_k chain + stores, [12] waiting for the TRSM warps, [13] rhs update
+// phase A as the first TRSM warp of CTA 0 sees it: [0] row loads + look-ahead fold, [1] waiting
+// for L11, [2] TRSM + row stores, [3] waiting for y_k + rhs update  -> g_coop_prof[11,12,14,15]
+#define COOP_TTICK(slot)                                  \
+  do {                                                    \
+    if (blockIdx.x == 0 && threadIdx.x == 32) {           \
+      const long long now_ = clock64();                   \
+      tprof[slot] += now_ - tprof_t;                      \
+      tprof_t = now_;                                     \
+    }                                                     \
+  } while (0)
+
 #define COOP_ATICK(slot)                                  \
   do {                                                    \
     if (blockIdx.x == 0 && threadIdx.x == 0) {            \
@@ -44,7 +55,13 @@ __device__ long long g_coop_prof[16];  // [8..13]: phase A split of CTA 0, see C
 
 constexpr int kCoopThreads = 256;
 constexpr int kLdStride = kPB * (kPB + 1);  // per panel in `ldiag`: L11 (kPB x kPB) + 1/diag (kPB)
-constexpr int kTrsmRows = 128;  // panel rows per CTA in phase A (warps 1..4, one row per thread)
+// Panel rows per CTA in phase A, one row per thread of the TRSM warps.  The rows carry almost all
+// of the fp64 work of a panel step (look-ahead fold 1024 DFMA per row, TRSM 528), and fp64 issues
+// at ~2.2 cycles per warp instruction per scheduler on B200: with 128 rows per CTA (4 warps, two
+// of them on one scheduler) the row path took 12.5 us per panel and the POTRF warp waited for
+// it.  64 rows on two warps with a scheduler each halve that and double the panel CTAs.
+constexpr int kTrsmWarps = 2;
+constexpr int kTrsmRows = 32 * kTrsmWarps;
 
 // 1/sqrt(d) to fp64 accuracy from the fp32 MUFU.RSQ seed and two Newton steps: this sits on
 // the pivot chain of the factorisation (D sequential pivots), so its latency matters.
@@ -196,12 +213,15 @@ __global__ void __launch_bounds__(kCoopThreads)
   long long prof_acc[6] = {0, 0, 0, 0, 0, 0};
   long long prof_t = clock64();
   long long aprof[6] = {0, 0, 0, 0, 0, 0};
+  long long tprof[4] = {0, 0, 0, 0};  // thread 32 (first TRSM warp) of CTA 0, see COOP_TTICK
+  long long tprof_t = 0;
   long long aprof_t = 0;
   __syncthreads();
   // warp roles in phase A: 0 = POTRF (alone on its scheduler: warp 4 idles), 1,2,3,6 = the
   // CTA's 128 panel rows (look-ahead update, TRSM, rhs), 5 = forward-substitution chain y_k
-  const bool trsm_warp = (warp >= 1 && warp <= 3) || warp == 6;
-  const int trsm_slot = (warp == 6) ? 3 : warp - 1;
+  const bool trsm_warp = warp >= 1 && warp <= kTrsmWarps;  // warps 1, 2: schedulers 1, 2
+  const int trsm_slot = warp - 1;
+  const bool diag_warp = warp == 0 || warp == 4 || warp == 5 || warp == 7;
 
   for (int k0 = 0; k0 < D; k0 += kPB) {
     const int pb = min(kPB, D - k0);
@@ -219,7 +239,7 @@ __global__ void __launch_bounds__(kCoopThreads)
       const int nrows = max(0, min(kTrsmRows, D - row0));
       // named barrier 1 ("L11 ready"): warp 0 arrives; the TRSM warps, the y_k warp and, on the
       // CTA that keeps the diagonal blocks for the backward phase, the inverse warp wait
-      const int bar1 = (rc == 0) ? 224 : 192;
+      const int bar1 = 64 + 32 * kTrsmWarps + ((rc == 0) ? 32 : 0);
       // 1. what the POTRF needs (diagonal block, the previous panel's rows of it, rhs) by all
       //    threads; the CTA's 128 panel rows are loaded by the TRSM warps themselves AFTER this
       //    barrier, beside the diagonal-block update and the POTRF instead of in front of them
@@ -235,16 +255,21 @@ __global__ void __launch_bounds__(kCoopThreads)
       if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
       __syncthreads();
       COOP_ATICK(8);
-      if (trsm_warp) {
-        const int tt = trsm_slot * 32 + lane;
-#pragma unroll 8
+      if (blockIdx.x == 0 && t == 32) tprof_t = clock64();
+      // the row loads are shared with the two warps that have nothing else to do (3 and 6): one
+      // batch of 32 independent loads per thread instead of eight dependent batches
+      const bool load_warp = trsm_warp || warp == 3 || warp == 6;
+      if (load_warp) {
+        const int tt = (trsm_warp ? trsm_slot : (warp == 3 ? 2 : 3)) * 32 + lane;
+#pragma unroll
         for (int x = tt; x < kTrsmRows * kPB; x += 128) {
           const int r = x / kPB, c = x % kPB;
           const size_t g = static_cast<size_t>(row0 + r) * D;
           S.u.a.Xr[r][c] = (r < nrows && c < pb) ? A[g + k0 + c] : 0.0;
           S.u.a.Lp[r][c] = (la && r < nrows) ? A[g + kp + c] : 0.0;
         }
-        asm volatile("bar.sync 4, 128;");  // the four TRSM warps: rows staged
+        if (trsm_warp) asm volatile("bar.sync 4, 128;");  // rows staged
+        else asm volatile("bar.arrive 4, 128;");
       }
       // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
       //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
@@ -252,7 +277,7 @@ __global__ void __launch_bounds__(kCoopThreads)
       //    dimension; the halves meet in shared memory.  Entries above the diagonal receive
       //    garbage and are never read.  (The first version gave every thread 4 outputs of one
       //    row: 5 shared loads per 4 DFMA, 4.2 us per panel on the critical path.)
-      if (la && !trsm_warp) {
+      if (la && diag_warp) {
         double acc[4][4];
         const int u = ((warp == 0) ? 0 : (warp == 4) ? 1 : (warp == 5) ? 2 : 3) * 32 + lane;
         const int tile = u & 63, half = u >> 6;
@@ -272,7 +297,7 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int k = 0; k < 4; k++) acc[i][k] += av[i].x * bv[k].x + av[i].y * bv[k].y;
+            for (int k = 0; k < 4; k++) acc[i][k] = fma(av[i].y, bv[k].y, fma(av[i].x, bv[k].x, acc[i][k]));
         }
         if (half == 1) {
 #pragma unroll
@@ -317,11 +342,14 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
             for (int c = 0; c < kPB; c++) {
               const double2 b2 = *reinterpret_cast<const double2 *>(&S.Ls[c][j]);
-              x[c] -= lp.x * b2.x + lp.y * b2.y;
+              x[c] = fma(-lp.y, b2.y, fma(-lp.x, b2.x, x[c]));  // two DFMA (a sum of products costs three)
             }
           }
         }
+        COOP_TTICK(0);
+        const double rhs_old = has_row ? rhs[row] : 0.0;  // in flight during the TRSM
         asm volatile("bar.sync 1, %0;" ::"r"(bar1));
+        COOP_TTICK(1);
         // right-looking TRSM: independent updates per column -> ILP
 #pragma unroll
         for (int c = 0; c < kPB; c++) {
@@ -336,13 +364,18 @@ __global__ void __launch_bounds__(kCoopThreads)
           for (int c = 0; c < kPB; c++)
             if (c < pb) Ar[c] = x[c];
         }
-        asm volatile("bar.sync 2, 160;");  // y_k ready
+        COOP_TTICK(2);
+        asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));  // y_k ready
         if (has_row) {
-          double dot = 0.0;
+          double d0 = 0.0, d1 = 0.0, d2 = 0.0, d3 = 0.0;
 #pragma unroll
-          for (int c = 0; c < kPB; c++) dot += x[c] * yk[c];
-          rhs[row] -= dot;
+          for (int c = 0; c < kPB; c += 4) {
+            d0 += x[c] * yk[c], d1 += x[c + 1] * yk[c + 1];
+            d2 += x[c + 2] * yk[c + 2], d3 += x[c + 3] * yk[c + 3];
+          }
+          rhs[row] = rhs_old - ((d0 + d1) + (d2 + d3));
         }
+        COOP_TTICK(3);
       } else if (warp == 5) {
         // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp
         asm volatile("bar.sync 1, %0;" ::"r"(bar1));
@@ -358,7 +391,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         }
         __syncwarp();
         if (lane >= pb) yk[lane] = 0.0;
-        asm volatile("bar.sync 2, 160;");
+        asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));
         if (rc == 0 && lane < pb) xbuf[k0 + lane] = mine;
       } else if (warp == 4 && rc == 0) {
         // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot
@@ -529,5 +562,9 @@ __global__ void __launch_bounds__(kCoopThreads)
     for (int k = 0; k < 6; k++) g_coop_prof[k] += prof_acc[k];
     for (int k = 0; k < 6; k++) g_coop_prof[8 + k] += aprof[k];
     g_coop_prof[6] += 1;
+  }
+  if (t == 32) {
+    g_coop_prof[11] += tprof[0], g_coop_prof[12] += tprof[1];
+    g_coop_prof[14] += tprof[2], g_coop_prof[15] += tprof[3];
   }
 }

@@ -55,7 +55,8 @@ def coop_profile():
     _lib.lib.m3r_debug_coop_profile(out)
     n = max(out[6], 1)
     names = ["phaseA", "sync1", "phaseB", "sync2", "backward", "finish", "launches", "-", "A:loads", "A:diag update",
-             "A:potrf", "-", "-", "A:trsm+rhs (to CTA barrier)"]
+             "A:potrf", "T:row loads + fold", "T:wait for L11", "A:wait for the TRSM warps", "T:trsm + row stores",
+             "T:wait y_k + rhs update"]
     print(f"coop solver: {out[6]} launches, solve_ms {r['solve_ms']:.3f}, linearize_ms {r['linearize_ms']:.3f}")
     for k, nm in enumerate(names):
         if nm not in ("launches", "-"):
