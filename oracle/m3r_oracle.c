@@ -96,6 +96,34 @@ static inline void clampf(float *x, const float lo, const float hi) {
   *x = fminf(fmaxf(*x, lo), hi);
 }
 
+/* Rounding.  The reference is compiled by nvcc with its default -fmad=true, so which products
+ * are rounded on their own and which are fused into the following add is part of what its
+ * binary computes.  The sequence below is the one nvcc 12.9 emits for these expressions
+ * (read off the FFMA / FMUL / FADD order of the compiled kernel, oracle/_ref, and of this
+ * repo's own kernel, which agree); this file is built with -ffp-contract=off, so every fusion
+ * is an explicit fmaf and nothing else is contracted:
+ *   a0*b0 + a1*b1 + a2*b2         ->  fma(a2,b2, fma(a0,b0, a1*b1))     (dot3)
+ *   w11*x11 + w12*x12 + ...       ->  fma(w22,x22, fma(w21,x21, fma(w11,x11, w12*x12)))
+ *   r[j]*inv - pt[j]              ->  fma(r[j], inv, -pt[j])            (r[j] *= inv is not rounded)
+ *   A00*A11 - A01*A01             ->  fma(A00,A11, -(A01*A01))
+ *   A11*b0 - A01*b1               ->  fma(-A01,b1, A11*b0)
+ *   -A01*b0 + A00*b1              ->  fma(-A01,b0, A00*b1)
+ *   u + det_inv*(...)             ->  fma(..., det_inv, u)
+ * The double-promoted pieces (`1.0 - du`, `1.0 / x`, `lambda *= 0.1`) are kept as written;
+ * du is a multiple of 2^-23, so (1.0 - du)*dv rounds once either way.  On smooth scenes the
+ * contraction is invisible (match_a/b.npz were reproduced bit for bit without it); on chaotic
+ * inputs (tests/golden/mast3r_rand.npz: 4 % of the iterations converge) an uncontracted build
+ * leaves the reference's orbit on 0.4 % of the pixels, this one on none
+ * (tests/test_matching_gpu.py::test_oracle_twin_of_reference_cuda). */
+static inline float dot3c(const float *a, const float *b) {
+  return fmaf(a[2], b[2], fmaf(a[0], b[0], a[1] * b[1]));
+}
+
+static inline float bilerp(float w11, float w12, float w21, float w22, float x11, float x12,
+                           float x21, float x22) {
+  return fmaf(w22, x22, fmaf(w21, x21, fmaf(w11, x11, w12 * x12)));
+}
+
 static void iter_proj_point(const float *img /* [h,w,9] of batch b */, const float *pt,
                             const float *pinit, float *pout, uint8_t *conv, int h, int w,
                             int max_iter, float lambda_init, float cost_thresh) {
@@ -123,33 +151,30 @@ static void iter_proj_point(const float *img /* [h,w,9] of batch b */, const flo
     const float *r12 = img + ((size_t)(v11 + 1) * w + u11) * c;
     const float *r21 = img + ((size_t)v11 * w + (u11 + 1)) * c;
     const float *r22 = img + ((size_t)v11 * w + u11) * c;
-    for (int j = 0; j < 3; j++) r[j] = w11 * r11[j] + w12 * r12[j] + w21 * r21[j] + w22 * r22[j];
-    for (int j = 3; j < 6; j++)
-      gx[j - 3] = w11 * r11[j] + w12 * r12[j] + w21 * r21[j] + w22 * r22[j];
-    for (int j = 6; j < 9; j++)
-      gy[j - 6] = w11 * r11[j] + w12 * r12[j] + w21 * r21[j] + w22 * r22[j];
+    for (int j = 0; j < 3; j++) r[j] = bilerp(w11, w12, w21, w22, r11[j], r12[j], r21[j], r22[j]);
+    for (int j = 3; j < 6; j++) gx[j - 3] = bilerp(w11, w12, w21, w22, r11[j], r12[j], r21[j], r22[j]);
+    for (int j = 6; j < 9; j++) gy[j - 6] = bilerp(w11, w12, w21, w22, r11[j], r12[j], r21[j], r22[j]);
     /* :186-191 */
-    float r_norm = sqrtf(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+    float r_norm = sqrtf(dot3c(r, r));
     float r_norm_inv = 1.0 / r_norm;
-    for (int j = 0; j < 3; j++) r[j] *= r_norm_inv;
     /* :195-198 */
-    for (int j = 0; j < 3; j++) err[j] = r[j] - pt[j];
-    float cost = err[0] * err[0] + err[1] * err[1] + err[2] * err[2];
+    for (int j = 0; j < 3; j++) err[j] = fmaf(r[j], r_norm_inv, -pt[j]);
+    float cost = dot3c(err, err);
     /* :202-210 */
-    float A00 = gx[0] * gx[0] + gx[1] * gx[1] + gx[2] * gx[2];
-    float A01 = gx[0] * gy[0] + gx[1] * gy[1] + gx[2] * gy[2];
-    float A11 = gy[0] * gy[0] + gy[1] * gy[1] + gy[2] * gy[2];
-    float b0 = -(err[0] * gx[0] + err[1] * gx[1] + err[2] * gx[2]);
-    float b1 = -(err[0] * gy[0] + err[1] * gy[1] + err[2] * gy[2]);
+    float A00 = dot3c(gx, gx);
+    float A01 = dot3c(gx, gy);
+    float A11 = dot3c(gy, gy);
+    float b0 = -dot3c(err, gx);
+    float b1 = -dot3c(err, gy);
     A00 += lambda;
     A11 += lambda;
     /* :213-215 */
-    float det_inv = 1.0 / (A00 * A11 - A01 * A01);
-    float delta_u = det_inv * (A11 * b0 - A01 * b1);
-    float delta_v = det_inv * (-A01 * b0 + A00 * b1);
+    float det_inv = 1.0 / fmaf(A00, A11, -(A01 * A01));
+    float num_u = fmaf(-A01, b1, A11 * b0);
+    float num_v = fmaf(-A01, b0, A00 * b1);
     /* :218-221 */
-    float u_new = u + delta_u;
-    float v_new = v + delta_v;
+    float u_new = fmaf(num_u, det_inv, u);
+    float v_new = fmaf(num_v, det_inv, v);
     clampf(&u_new, 1, w - 2);
     clampf(&v_new, 1, h - 2);
     /* :225-233 */
@@ -166,12 +191,11 @@ static void iter_proj_point(const float *img /* [h,w,9] of batch b */, const flo
     r21 = img + ((size_t)v11 * w + (u11 + 1)) * c;
     r22 = img + ((size_t)v11 * w + u11) * c;
     /* :241-256 */
-    for (int j = 0; j < 3; j++) r[j] = w11 * r11[j] + w12 * r12[j] + w21 * r21[j] + w22 * r22[j];
-    r_norm = sqrtf(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+    for (int j = 0; j < 3; j++) r[j] = bilerp(w11, w12, w21, w22, r11[j], r12[j], r21[j], r22[j]);
+    r_norm = sqrtf(dot3c(r, r));
     r_norm_inv = 1.0 / r_norm;
-    for (int j = 0; j < 3; j++) r[j] *= r_norm_inv;
-    for (int j = 0; j < 3; j++) err[j] = r[j] - pt[j];
-    float new_cost = err[0] * err[0] + err[1] * err[1] + err[2] * err[2];
+    for (int j = 0; j < 3; j++) err[j] = fmaf(r[j], r_norm_inv, -pt[j]);
+    float new_cost = dot3c(err, err);
     /* :259-268 */
     if (new_cost < cost) {
       u = u_new;

@@ -273,6 +273,34 @@ def test_golden_front_end(oracle, path):
     assert torch.equal(valid, torch.from_numpy(z["ref_valid"]))
 
 
+def test_golden_random_init_network(oracle):
+    """The production network with seeded random weights as the input distribution
+    (tests/golden/make_golden_mast3r.py): near-degenerate rays, 4 % of the LM runs converge,
+    descriptor scores without a clear maximum.  The oracle restatement must reproduce the
+    reference's matching.py on these values exactly as on the smooth scenes."""
+    path = os.path.join(GOLD, "mast3r_rand.npz")
+    if not os.path.exists(path):
+        pytest.skip("no random-init network vectors committed")
+    z = np.load(path)
+    X11, X21 = torch.from_numpy(z["X11"]), torch.from_numpy(z["X21"])
+    D11 = torch.from_numpy(z["D11_f16"]).view(torch.float16)
+    D21 = torch.from_numpy(z["D21_f16"]).view(torch.float16)
+    # the head ranges the fixture is supposed to carry (catmlp_dpt_head.py:17-38, postprocess.py:49-58)
+    assert z["C11"].min() >= 1.0 and z["C21"].min() >= 1.0
+    assert z["Q11"].min() >= 0.0 and z["Q21"].min() >= 0.0
+    assert abs(float(D11.float().norm(dim=-1).mean()) - 1.0) < 1e-3
+    rays, pts, p_init = oracle.prep_for_iter_proj(X11, X21, None)
+    assert torch.equal(rays, torch.from_numpy(z["ref_rays"]))
+    cfg = {k: z[k].item() for k in ("max_iter", "lambda_init", "convergence_thresh", "dist_thresh",
+                                    "radius", "dilation_max")}
+    p, conv = oracle.iter_proj(rays, pts, p_init, cfg["max_iter"], cfg["lambda_init"], cfg["convergence_thresh"])
+    assert torch.equal(p, torch.from_numpy(z["ref_p_proj"]))
+    assert torch.equal(conv, torch.from_numpy(z["ref_converged"]))
+    idx, valid = oracle.match(X11, X21, D11, D21, None, **cfg)
+    assert torch.equal(idx, torch.from_numpy(z["ref_idx"]))
+    assert torch.equal(valid, torch.from_numpy(z["ref_valid"]))
+
+
 TRACK_KEYS = ("max_iters", "rel_error", "delta_norm", "huber", "sigma_ray", "sigma_dist", "sigma_pixel",
               "sigma_depth", "pixel_border", "depth_eps")
 
