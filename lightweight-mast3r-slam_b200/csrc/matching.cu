@@ -534,11 +534,16 @@ __global__ void __launch_bounds__(kRefineThreads)
 // out-of-image rows are simply never written); otherwise that warp runs the level with the
 // checked per-candidate path from global memory.  Same candidates, same order, same
 // arithmetic: results are identical either way.
-constexpr int kRtQ = 16;                    // query tile edge
-constexpr int kRtT = 48;                    // staged box edge (texels)
-constexpr int kRtThreads = kRtQ * kRtQ;     // 256
+#ifndef M3R_RT_QY
+#define M3R_RT_QY 16  // measured at 512x384: 16x8 153.5, 16x12 148.9, 16x16 145.4 us (profiles/r1_b_matching_ncu_full.md)
+#endif
+constexpr int kRtQ = 16;                    // query tile width
+constexpr int kRtQy = M3R_RT_QY;            // query tile height
+constexpr int kRtT = 48;                    // staged box width (texels): 16 + 2*15 + slack
+constexpr int kRtTy = kRtQy + 32;           // staged box height
+constexpr int kRtThreads = kRtQ * kRtQy;
 constexpr int kRtRowU4 = 3;                 // uint4 per 24-half descriptor row
-constexpr int kRtTileBytes = kRtT * kRtT * kRtRowU4 * 16;
+constexpr int kRtTileBytes = kRtT * kRtTy * kRtRowU4 * 16;
 constexpr int kRtSmemBytes = kRtTileBytes + 64;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -579,7 +584,7 @@ __global__ void __launch_bounds__(kRtThreads, 2)
   constexpr int radius = 3, nside = 7;
   const int tid = threadIdx.x, lane = tid & 31;
   const int qx = blockIdx.x * kRtQ + (tid & (kRtQ - 1));
-  const int qy = blockIdx.y * kRtQ + (tid >> 4);
+  const int qy = blockIdx.y * kRtQy + (tid >> 4);
   const int b = blockIdx.z;
   const bool active = (qx < w) && (qy < h);
   const size_t n = static_cast<size_t>(h) * w;
@@ -612,9 +617,9 @@ __global__ void __launch_bounds__(kRtThreads, 2)
   const bool any_live = red[0] != INT_MAX;
   // staged box [ou, ou+T) x [ov, ov+T), centred on the bounding box of the CTA's matches
   const int ou = any_live ? ((red[0] + red[1] + 1 - kRtT) >> 1) : 0;
-  const int ov = any_live ? ((red[2] + red[3] + 1 - kRtT) >> 1) : 0;
+  const int ov = any_live ? ((red[2] + red[3] + 1 - kRtTy) >> 1) : 0;
   const int c0 = max(ou, 0), c1 = min(ou + kRtT, w);  // columns of the box inside the image
-  const int r0 = max(ov, 0), r1 = min(ov + kRtT, h);
+  const int r0 = max(ov, 0), r1 = min(ov + kRtTy, h);
   const bool have_box = any_live && c1 > c0 && r1 > r0;
   const __half *img_h = D11 + static_cast<size_t>(b) * n * 24;
   if (tid < 32 && have_box) {
@@ -668,7 +673,7 @@ __global__ void __launch_bounds__(kRtThreads, 2)
   for (int d = dilation_max; d > 0; d--) {
     const int rd = radius * d;
     const bool inside = have_box && (u0 - rd >= ou) && (u0 + rd < ou + kRtT) && (v0 - rd >= ov) &&
-                        (v0 + rd < ov + kRtT) && (6 * d < kRtT);
+                        (v0 + rd < ov + kRtTy) && (6 * d < kRtTy);
     if (!__any_sync(0xffffffffu, live)) break;  // nothing to do in this warp (no barriers below)
     if (__all_sync(0xffffffffu, inside || !live)) {
       // ---- whole warp inside the staged box: unrolled, unchecked loads from shared memory
@@ -831,7 +836,7 @@ static int launch_refine_tiled(const __half *D11, const __half *D21, const long 
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
     attr_set = true;
   }
-  const dim3 tgrid((w + kRtQ - 1) / kRtQ, (h + kRtQ - 1) / kRtQ, b);
+  const dim3 tgrid((w + kRtQ - 1) / kRtQ, (h + kRtQy - 1) / kRtQy, b);
   M3R_REQUIRE(tgrid.y <= 65535, "refine_matches: image too tall");
   refine_f16_tiled_kernel<<<tgrid, kRtThreads, kRtSmemBytes, s>>>(D11, D21, p1, p1_new, lin_out, h, w,
                                                                  dilation_max);

@@ -1,3 +1,4 @@
-set -x
-timeout 1500 python -m pytest tests/test_matching_gpu.py tests/test_front_gpu.py -m gpu -q -x -s -k "random_init or oracle_twin" > gpurun_out/pytest_rand.log 2>&1; echo "pytest rc=$?"
-grep -E "bit-identical|agreement|passed|failed|Error|^E " gpurun_out/pytest_rand.log | head -60
+for v in tools/_var_qy8.so "" tools/_var_qy16.so; do
+  if [ -n "$v" ]; then export M3R_B200_LIB=$PWD/$v; else unset M3R_B200_LIB; fi
+  timeout 300 python tools/refine_var.py 2>&1 | tail -1
+done
