@@ -572,6 +572,15 @@ __device__ __forceinline__ __half2 score_pair(const uint4 *ra, const uint4 *rb,
   return acc;
 }
 
+#ifdef M3R_RT_PROF  // experiments only (tools/refine_prof.py): per-CTA timeline of this kernel
+__device__ unsigned long long g_rt_prof[4096 * 16];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#endif
+
 __global__ void __launch_bounds__(kRtThreads, 2)
     refine_f16_tiled_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
                             const long long *__restrict__ p1, long long *__restrict__ p1_new,
@@ -590,6 +599,15 @@ __global__ void __launch_bounds__(kRtThreads, 2)
   const size_t n = static_cast<size_t>(h) * w;
   const size_t gi = static_cast<size_t>(b) * n + static_cast<size_t>(qy) * w + qx;
 
+#ifdef M3R_RT_PROF
+  unsigned long long *prof = g_rt_prof + ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) % 4096 * 16;
+  int n_fallback = 0;
+  if (tid == 0) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    prof[0] = smid, prof[1] = gtime();
+  }
+#endif
   if (tid == 0) {
     red[0] = INT_MAX, red[1] = INT_MIN, red[2] = INT_MAX, red[3] = INT_MIN;
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
@@ -667,6 +685,9 @@ __global__ void __launch_bounds__(kRtThreads, 2)
     }
   }
 
+#ifdef M3R_RT_PROF
+  if (tid == 0) prof[2] = gtime();
+#endif
   const uint4 *img = reinterpret_cast<const uint4 *>(img_h);
   __half max_score = __ushort_as_half(0);  // +0 (see the contract above)
   int u_new = u0, v_new = v0;
@@ -710,6 +731,9 @@ __global__ void __launch_bounds__(kRtThreads, 2)
         v_new = v0 - rd + bj * d;
       }
     } else if (live) {
+#ifdef M3R_RT_PROF
+      n_fallback++;
+#endif
       // ---- checked path from global memory (a window leaves the box)
       for (int c = 0; c < nside * nside; c += 2) {
         const int ia = c / nside, ja = c - ia * nside;
@@ -738,6 +762,12 @@ __global__ void __launch_bounds__(kRtThreads, 2)
     if (p1_new) reinterpret_cast<longlong2 *>(p1_new)[gi] = res;
     if (lin_out) lin_out[gi] = res.x + static_cast<long long>(w) * res.y;  // pixel_to_lin (matching.py:88)
   }
+#ifdef M3R_RT_PROF
+  __syncwarp();
+  if (lane == 0) prof[3 + (tid >> 5)] = gtime();
+  const int nf = __reduce_max_sync(0xffffffffu, n_fallback);  // levels this warp ran from global memory
+  if (lane == 0 && nf) atomicAdd(prof + 15, static_cast<unsigned long long>(nf));
+#endif
 }
 
 // Generic path: any fdim, any of the three dtypes; accumulation in T as the reference does.
@@ -843,6 +873,16 @@ static int launch_refine_tiled(const __half *D11, const __half *D21, const long 
   M3R_LAUNCH_CHECK("refine_f16_tiled_kernel");
   return M3R_OK;
 }
+
+#ifdef M3R_RT_PROF
+extern "C" int m3r_debug_refine_profile(unsigned long long *out, int n_entries) {
+  M3R_CUDA_TRY(cudaDeviceSynchronize());
+  M3R_CUDA_TRY(cudaMemcpyFromSymbol(out, g_rt_prof, sizeof(unsigned long long) * n_entries));
+  static unsigned long long zero[4096 * 16];
+  M3R_CUDA_TRY(cudaMemcpyToSymbol(g_rt_prof, zero, sizeof(zero)));
+  return M3R_OK;
+}
+#endif
 
 extern "C" int m3r_iter_proj_v(const float *rays, const float *pts, const float *p_init,
                                float *p_new, uint8_t *converged, int b, int h, int w, int n,

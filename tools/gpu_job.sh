@@ -1,4 +1,3 @@
-for v in tools/_var_qy8.so "" tools/_var_qy16.so; do
-  if [ -n "$v" ]; then export M3R_B200_LIB=$PWD/$v; else unset M3R_B200_LIB; fi
-  timeout 300 python tools/refine_var.py 2>&1 | tail -1
-done
+timeout 600 python -m pytest tests/test_matching_gpu.py tests/test_front_gpu.py -m gpu -q -x > gpurun_out/pytest_match.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_match.log
+timeout 300 python tools/kbench.py 2>&1 | grep refine | head -2
+timeout 300 python tools/kbench.py 2>&1 | grep refine | head -2
