@@ -581,10 +581,63 @@ __device__ __forceinline__ unsigned long long gtime() {
 }
 #endif
 
+// Plan pass (one warp per tile, ~4 us at 512x384): the bounding box of each tile's matches and
+// a "heavy" flag.  The timeline of the tiled kernel (profiles/r1_n_refine_timeline.md) shows
+// that a launch ends when its slowest tiles end: tiles whose matches collapsed onto the image
+// border (view-2 pixels that see nothing of view 1, clamped by iter_proj) live 2.5-3x as long as
+// the others, because their searches fan out of any box, and one of them starting in the last
+// round holds an SM for 100 us while the rest of the machine idles.  The planned kernel
+// therefore takes the heavy tiles first (longest-processing-time-first list scheduling, the
+// order computed by every CTA from the flag array), and reads its box from the plan instead of
+// reducing it, so the TMA copies start at the first instruction instead of after a dependent
+// p1 load and two barriers.
+constexpr int kRtMaxPlanned = 4096;  // tiles; above this the unplanned grid-of-tiles launch is used
+__global__ void __launch_bounds__(kRtThreads)
+    refine_plan_kernel(const long long *__restrict__ p1, int4 *__restrict__ plan,
+                       unsigned char *__restrict__ heavy, int h, int w, int dilation_max, int tiles_x,
+                       int tiles_y) {
+  // one CTA per tile, one query per thread: every load of the pass is in flight at once
+  __shared__ int red[5];
+  const int t = blockIdx.x, tid = threadIdx.x;
+  const int per_img = tiles_x * tiles_y;
+  const int b = t / per_img, r = t - b * per_img;
+  const int ty = r / tiles_x, tx = r - ty * tiles_x;
+  const long long reach = 3LL * dilation_max;
+  const int qx = tx * kRtQ + (tid & (kRtQ - 1)), qy = ty * kRtQy + (tid >> 4);
+  if (tid == 0) red[0] = INT_MAX, red[1] = INT_MIN, red[2] = INT_MAX, red[3] = INT_MIN, red[4] = 0;
+  bool live = false;
+  int u = 0, v = 0;
+  if (qx < w && qy < h) {
+    const longlong2 p = reinterpret_cast<const longlong2 *>(
+        p1)[static_cast<size_t>(b) * h * w + static_cast<size_t>(qy) * w + qx];
+    live = !(p.x < -reach || p.x >= w + reach || p.y < -reach || p.y >= h + reach);
+    u = static_cast<int>(p.x), v = static_cast<int>(p.y);
+  }
+  __syncthreads();
+  const int umin = __reduce_min_sync(0xffffffffu, live ? u : INT_MAX);
+  const int umax = __reduce_max_sync(0xffffffffu, live ? u : INT_MIN);
+  const int vmin = __reduce_min_sync(0xffffffffu, live ? v : INT_MAX);
+  const int vmax = __reduce_max_sync(0xffffffffu, live ? v : INT_MIN);
+  const int cnt = __popc(__ballot_sync(0xffffffffu, live));
+  if ((tid & 31) == 0 && cnt) {
+    atomicMin(&red[0], umin), atomicMax(&red[1], umax), atomicMin(&red[2], vmin), atomicMax(&red[3], vmax);
+    atomicAdd(&red[4], cnt);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    plan[t] = make_int4(red[0], red[1], red[2], red[3]);
+    // collapsed: many matches on a span far below the tile's own 16 pixels
+    heavy[t] = (red[4] >= kRtThreads / 4 && (red[1] - red[0] < kRtQ / 2 || red[3] - red[2] < kRtQy / 2)) ? 1 : 0;
+  }
+}
+
+template <bool PLANNED>
 __global__ void __launch_bounds__(kRtThreads, 2)
     refine_f16_tiled_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
                             const long long *__restrict__ p1, long long *__restrict__ p1_new,
-                            long long *__restrict__ lin_out, int h, int w, int dilation_max) {
+                            long long *__restrict__ lin_out, int h, int w, int dilation_max,
+                            const int4 *__restrict__ plan, const unsigned char *__restrict__ heavy,
+                            int tiles_x, int tiles_y, int ntiles) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint4 *tile = reinterpret_cast<uint4 *>(smem_raw);
   unsigned long long *mbar = reinterpret_cast<unsigned long long *>(smem_raw + kRtTileBytes);
@@ -592,15 +645,71 @@ __global__ void __launch_bounds__(kRtThreads, 2)
 
   constexpr int radius = 3, nside = 7;
   const int tid = threadIdx.x, lane = tid & 31;
-  const int qx = blockIdx.x * kRtQ + (tid & (kRtQ - 1));
-  const int qy = blockIdx.y * kRtQy + (tid >> 4);
-  const int b = blockIdx.z;
+  int tile_x = blockIdx.x, tile_y = blockIdx.y, b = blockIdx.z;
+  int4 box = make_int4(INT_MAX, INT_MIN, INT_MAX, INT_MIN);
+  if (PLANNED) {
+    // this CTA's tile: the blockIdx.x-th entry of (heavy tiles in index order, then the others).
+    // Every thread owns 16 consecutive flags; a block-wide prefix sum of the heavy counts finds
+    // the owner of the wanted rank.
+    int *scan = red;  // [0..7] warp totals, [8] the tile
+    const int first_id = tid * 16;
+    const int nvalid = min(max(ntiles - first_id, 0), 16);
+    uint4 f = make_uint4(0u, 0u, 0u, 0u);
+    if (nvalid > 0) f = reinterpret_cast<const uint4 *>(heavy)[tid];
+    const uint32_t fw[4] = {f.x, f.y, f.z, f.w};
+    unsigned bits = 0;  // bit k = flag of tile first_id + k
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      if (k < nvalid && ((fw[k >> 2] >> (8 * (k & 3))) & 0xffu) != 0) bits |= 1u << k;
+    }
+    const int hv = __popc(bits);
+    int incl = hv;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) scan[tid >> 5] = incl;
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < kRtThreads / 32; k++) {
+      const int v = scan[k];
+      before += (k < (tid >> 5)) ? v : 0;
+      total += v;
+    }
+    const int hp = before + incl - hv;              // heavy tiles before my 16
+    const int lp = min(first_id, ntiles) - hp;      // light tiles before my 16
+    const int c = blockIdx.x;
+    unsigned pick = 0;
+    int want = -1;
+    if (c < total) {
+      if (c >= hp && c < hp + hv) pick = bits, want = c - hp;
+    } else {
+      const int cl = c - total, nl = nvalid - hv;
+      if (cl >= lp && cl < lp + nl) pick = ~bits & ((1u << nvalid) - 1u), want = cl - lp;
+    }
+    if (want >= 0) {
+      for (int k = 0; k < want; k++) pick &= pick - 1;  // drop the `want` lowest set bits
+      scan[8] = first_id + __ffs(pick) - 1;
+    }
+    __syncthreads();
+    const int t = scan[8];
+    const int per_img = tiles_x * tiles_y;
+    b = t / per_img;
+    const int r = t - b * per_img;
+    tile_y = r / tiles_x, tile_x = r - tile_y * tiles_x;
+    box = plan[t];
+    __syncthreads();  // scan[] is red[]: re-initialised below
+  }
+  const int qx = tile_x * kRtQ + (tid & (kRtQ - 1));
+  const int qy = tile_y * kRtQy + (tid >> 4);
   const bool active = (qx < w) && (qy < h);
   const size_t n = static_cast<size_t>(h) * w;
   const size_t gi = static_cast<size_t>(b) * n + static_cast<size_t>(qy) * w + qx;
 
 #ifdef M3R_RT_PROF
-  unsigned long long *prof = g_rt_prof + ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) % 4096 * 16;
+  unsigned long long *prof = g_rt_prof + ((b * tiles_y + tile_y) * tiles_x + tile_x) % 4096 * 16;
   int n_fallback = 0;
   if (tid == 0) {
     unsigned smid;
@@ -621,8 +730,8 @@ __global__ void __launch_bounds__(kRtThreads, 2)
   const long long reach = static_cast<long long>(radius) * dilation_max;
   const bool live = active && !(p.x < -reach || p.x >= w + reach || p.y < -reach || p.y >= h + reach);
   int u0 = live ? static_cast<int>(p.x) : 0, v0 = live ? static_cast<int>(p.y) : 0;
-  __syncthreads();
-  {
+  __syncthreads();  // mbarrier initialised
+  if (!PLANNED) {
     const int a0 = __reduce_min_sync(0xffffffffu, live ? u0 : INT_MAX);
     const int a1 = __reduce_max_sync(0xffffffffu, live ? u0 : INT_MIN);
     const int a2 = __reduce_min_sync(0xffffffffu, live ? v0 : INT_MAX);
@@ -630,12 +739,13 @@ __global__ void __launch_bounds__(kRtThreads, 2)
     if (lane == 0 && a0 != INT_MAX) {
       atomicMin(&red[0], a0), atomicMax(&red[1], a1), atomicMin(&red[2], a2), atomicMax(&red[3], a3);
     }
+    __syncthreads();
+    box = make_int4(red[0], red[1], red[2], red[3]);
   }
-  __syncthreads();
-  const bool any_live = red[0] != INT_MAX;
+  const bool any_live = box.x != INT_MAX;
   // staged box [ou, ou+T) x [ov, ov+T), centred on the bounding box of the CTA's matches
-  const int ou = any_live ? ((red[0] + red[1] + 1 - kRtT) >> 1) : 0;
-  const int ov = any_live ? ((red[2] + red[3] + 1 - kRtTy) >> 1) : 0;
+  const int ou = any_live ? ((box.x + box.y + 1 - kRtT) >> 1) : 0;
+  const int ov = any_live ? ((box.z + box.w + 1 - kRtTy) >> 1) : 0;
   const int c0 = max(ou, 0), c1 = min(ou + kRtT, w);  // columns of the box inside the image
   const int r0 = max(ov, 0), r1 = min(ov + kRtTy, h);
   const bool have_box = any_live && c1 > c0 && r1 > r0;
@@ -856,20 +966,43 @@ using namespace m3r;
 
 static int launch_refine_tiled(const __half *D11, const __half *D21, const long long *p1,
                                long long *p1_new, long long *lin_out, int b, int h, int w,
-                               int dilation_max, cudaStream_t s) {
+                               int dilation_max, cudaStream_t s, bool planned = true) {
   static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
   int dev = 0;
   M3R_CUDA_TRY(cudaGetDevice(&dev));
   bool &attr_set = attr_set_dev[dev & 63];
   if (!attr_set) {
-    M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel,
+    M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel<false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
+    M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel<true>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
     attr_set = true;
   }
-  const dim3 tgrid((w + kRtQ - 1) / kRtQ, (h + kRtQy - 1) / kRtQy, b);
-  M3R_REQUIRE(tgrid.y <= 65535, "refine_matches: image too tall");
-  refine_f16_tiled_kernel<<<tgrid, kRtThreads, kRtSmemBytes, s>>>(D11, D21, p1, p1_new, lin_out, h, w,
-                                                                 dilation_max);
+  const int tiles_x = (w + kRtQ - 1) / kRtQ, tiles_y = (h + kRtQy - 1) / kRtQy;
+  const long long ntiles = static_cast<long long>(b) * tiles_x * tiles_y;
+  M3R_REQUIRE(tiles_y <= 65535, "refine_matches: image too tall");
+  if (planned && ntiles <= kRtMaxPlanned) {
+    // stream-ordered scratch: one int4 box per tile, then the flag bytes padded to 16 per thread
+    const size_t plan_bytes = static_cast<size_t>(ntiles) * sizeof(int4);
+    void *scratch = nullptr;
+    M3R_CUDA_TRY(cudaMallocAsync(&scratch, plan_bytes + kRtThreads * 16, s));
+    int4 *plan = static_cast<int4 *>(scratch);
+    unsigned char *heavy = static_cast<unsigned char *>(scratch) + plan_bytes;
+    const int nt = static_cast<int>(ntiles);
+    refine_plan_kernel<<<nt, kRtThreads, 0, s>>>(p1, plan, heavy, h, w, dilation_max, tiles_x, tiles_y);
+    g_launch_count.fetch_add(1, std::memory_order_relaxed);
+    refine_f16_tiled_kernel<true><<<nt, kRtThreads, kRtSmemBytes, s>>>(
+        D11, D21, p1, p1_new, lin_out, h, w, dilation_max, plan, heavy, tiles_x, tiles_y, nt);
+    const cudaError_t e = cudaGetLastError();
+    const cudaError_t ef = cudaFreeAsync(scratch, s);
+    g_launch_count.fetch_add(1, std::memory_order_relaxed);
+    if (e != cudaSuccess) return cuda_fail(e, "refine_f16_tiled_kernel<planned>");
+    if (ef != cudaSuccess) return cuda_fail(ef, "cudaFreeAsync");
+    return M3R_OK;
+  }
+  const dim3 tgrid(tiles_x, tiles_y, b);
+  refine_f16_tiled_kernel<false><<<tgrid, kRtThreads, kRtSmemBytes, s>>>(
+      D11, D21, p1, p1_new, lin_out, h, w, dilation_max, nullptr, nullptr, tiles_x, tiles_y, 0);
   M3R_LAUNCH_CHECK("refine_f16_tiled_kernel");
   return M3R_OK;
 }
@@ -939,11 +1072,11 @@ extern "C" int m3r_refine_matches_v(const void *D11, const void *D21, const int6
   long long *p1nl = reinterpret_cast<long long *>(p1_new);
   if (dtype == M3R_DTYPE_F16) {
     const bool fast = (fdim == 24) && aligned16(D11) && aligned16(D21) && variant != 1;
-    const bool tiled = fast && variant == 0 && radius == 3 && dilation_max >= 1 &&
+    const bool tiled = fast && (variant == 0 || variant == 3) && radius == 3 && dilation_max >= 1 &&
                        static_cast<long long>(n) == static_cast<long long>(h) * w;
-    if (tiled) {
+    if (tiled) {  // variant 3: the same kernel without the plan pass (grid of tiles in index order)
       const int rc = launch_refine_tiled(static_cast<const __half *>(D11), static_cast<const __half *>(D21),
-                                         p1l, p1nl, nullptr, b, h, w, dilation_max, s);
+                                         p1l, p1nl, nullptr, b, h, w, dilation_max, s, variant == 0);
       if (rc) return rc;
       return M3R_OK;
     } else if (fast) {

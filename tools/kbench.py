@@ -32,7 +32,7 @@ def main():
     for v in (0, 1):
         med, mn = timeit(lambda s: be.iter_proj(s["rays"], s["pts"], s["p_init"], 10, 1e-8, 1e-6, _variant=v), sets)
         print(f"iter_proj variant {v}: median {med:.1f} us, min {mn:.1f} us")
-    for v in (0, 2, 1):
+    for v in (0, 3, 2, 1):
         med, mn = timeit(lambda s: be.refine_matches(s["D11"], s["D21"], s["p1"], 3, 5, _variant=v), sets)
         print(f"refine_matches variant {v}: median {med:.1f} us, min {mn:.1f} us")
     for extra in sys.argv[1:]:
