@@ -182,7 +182,7 @@ def time_front_end(be, sets, M, steps, warmup):
         t1.record()
         torch.cuda.synchronize()
         out[name] = t0.elapsed_time(t1) / steps
-    out["fused_launches"] = 3
+    out["fused_launches"] = 4  # prep_rays, match_proj, refine_plan, refine
     out["fused_px_per_s"] = N_PTS / (out["fused_ms"] * 1e-3)
     return out
 
@@ -399,7 +399,7 @@ def time_frame_pipeline(sets, M, steps, warmup):
     torch.cuda.synchronize()
     ms = t0.elapsed_time(t1) / steps
     return {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "gpu_launches_per_frame": (_lib.launch_count() - l0) / steps,
-            "stages": "match(3) + match_confidence(1) + track_pose(1) + update_pointmap(1); memsets not counted",
+            "stages": "match(4) + match_confidence(1) + track_pose(1) + update_pointmap(1); memsets not counted",
             "torch_confidence_and_update_ms": torch_epi_ms,
             "torch_note": "the reference's torch lines for the confidence/fraction/unique epilogue and the weighted "
                           "keyframe update alone (wall clock, includes torch.unique's host sync); here they are two "
@@ -715,7 +715,7 @@ def main():
     r = time_matching(be, sets, M, args.steps, args.warmup, world)
     if args.profile:
         torch.cuda.profiler.stop()
-    launches = (_lib.launch_count() - l0) - 2 * args.warmup
+    launches = (_lib.launch_count() - l0) * args.steps // (args.steps + args.warmup)  # same launches every step
     clocks = sampler.stop()
     ms_step = r["total_ms"] / args.steps
     value = world * N_PTS / (ms_step * 1e-3)

@@ -8,6 +8,7 @@
 #include <cuda_fp16.h>
 
 #include <climits>
+#include <mutex>
 
 #include "m3r_common.cuh"
 
@@ -983,9 +984,29 @@ static int launch_refine_tiled(const __half *D11, const __half *D21, const long 
   M3R_REQUIRE(tiles_y <= 65535, "refine_matches: image too tall");
   if (planned && ntiles <= kRtMaxPlanned) {
     // stream-ordered scratch: one int4 box per tile, then the flag bytes padded to 16 per thread
+    // (from a private pool that keeps its memory across host synchronisations: the default
+    // pool's release threshold of 0 hands the pages back at every sync and the next allocation
+    // then costs hundreds of microseconds)
+    static cudaMemPool_t pools[64] = {nullptr};
+    static std::mutex pool_mu;
+    cudaMemPool_t pool;
+    {
+      std::lock_guard<std::mutex> lk(pool_mu);
+      if (!pools[dev & 63]) {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        M3R_CUDA_TRY(cudaMemPoolCreate(&pools[dev & 63], &props));
+        unsigned long long keep = ~0ull;
+        M3R_CUDA_TRY(cudaMemPoolSetAttribute(pools[dev & 63], cudaMemPoolAttrReleaseThreshold, &keep));
+      }
+      pool = pools[dev & 63];
+    }
     const size_t plan_bytes = static_cast<size_t>(ntiles) * sizeof(int4);
     void *scratch = nullptr;
-    M3R_CUDA_TRY(cudaMallocAsync(&scratch, plan_bytes + kRtThreads * 16, s));
+    M3R_CUDA_TRY(cudaMallocFromPoolAsync(&scratch, plan_bytes + kRtThreads * 16, pool, s));
     int4 *plan = static_cast<int4 *>(scratch);
     unsigned char *heavy = static_cast<unsigned char *>(scratch) + plan_bytes;
     const int nt = static_cast<int>(ntiles);

@@ -113,7 +113,8 @@ def test_refine_bit_exact_vs_oracle(backends, oracle, dtype, h, w, b, fdim, radi
 
 
 @pytest.mark.parametrize("h,w,b,kind", [(96, 128, 1, "random"), (96, 128, 2, "smooth"), (77, 101, 1, "smooth"),
-                                        (384, 512, 1, "smooth"), (50, 70, 1, "jumpy"), (16, 16, 1, "smooth")])
+                                        (384, 512, 1, "smooth"), (50, 70, 1, "jumpy"), (16, 16, 1, "smooth"),
+                                        (200, 328, 2, "collapsed"), (384, 512, 1, "collapsed")])
 def test_refine_kernels_agree(backends, oracle, h, w, b, kind):
     """Tiled (TMA-staged shared-memory box; planned heavy-first order by default, variant 3 = plain
     grid of tiles), direct-pair and generic kernels: same bits.
@@ -130,6 +131,9 @@ def test_refine_kernels_agree(backends, oracle, h, w, b, kind):
         if kind == "jumpy":  # a tenth of the matches are far from their neighbours'
             sel = (torch.rand(p1.shape[:2], generator=g) < 0.1).cuda()
             p1[sel] += torch.tensor([23, -19], device="cuda")
+        if kind == "collapsed":  # the right part of view 2 sees nothing of view 1: iter_proj's clamp
+            p1[..., 0] = (p1[..., 0] + w // 3).clamp(1, w - 2)  # puts those matches on the border column
+            p1[..., 1] = p1[..., 1].clamp(1, h - 2)  # ("heavy" tiles of the plan pass, taken first)
     p1 = p1.contiguous()
     outs = [backends.refine_matches(D11, D21, p1, 3, 5, _variant=v)[0] for v in (0, 1, 2, 3)]
     assert all(torch.equal(outs[0], o) for o in outs[1:])
@@ -140,6 +144,21 @@ def test_refine_kernels_agree(backends, oracle, h, w, b, kind):
         a = backends.refine_matches(D11, D21, p1, 3, dil, _variant=0)[0]
         c = backends.refine_matches(D11, D21, p1, 3, dil, _variant=1)[0]
         assert torch.equal(a, c), f"dilation_max={dil}"
+
+
+def test_refine_many_tiles(backends):
+    """More tiles than the plan pass orders (4096): the unplanned grid of tiles; and tile counts
+    that end inside a thread's group of 16 flags."""
+    for h, w, b in [(640, 656, 3), (16, 272, 1), (48, 528, 1)]:  # 4920, 17 and 99 tiles
+        g = torch.Generator().manual_seed(h + w)
+        D11 = torch.randn(b, h, w, 24, generator=g).half().cuda()
+        D21 = torch.randn(b, h * w, 24, generator=g).half().cuda()
+        vv, uu = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+        p1 = torch.stack([uu, vv], -1).view(1, h * w, 2).repeat(b, 1, 1)
+        p1 = (p1 + torch.randint(-3, 4, p1.shape, generator=g)).cuda().contiguous()
+        a = backends.refine_matches(D11, D21, p1, 3, 5, _variant=0)[0]
+        c = backends.refine_matches(D11, D21, p1, 3, 5, _variant=2)[0]
+        assert torch.equal(a, c), (h, w, b)
 
 
 def test_refine_edge_cases(backends, oracle):

@@ -1,3 +1,4 @@
-timeout 600 python -m pytest tests/test_matching_gpu.py -m gpu -q -x -k refine > gpurun_out/pytest_match.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_match.log
-timeout 300 python tools/kbench.py 2>&1 | grep refine | head -2
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:refine_plan -c 4 python tools/refine_var.py 2>&1 | grep -E "gpu__time_duration" | head -12
+timeout 900 python -m pytest tests/test_matching_gpu.py tests/test_front_gpu.py tests/test_streams_gpu.py -m gpu -q -x > gpurun_out/pytest_match.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_match.log
+python bench.py --skip-cpu --skip-refcuda > gpurun_out/bench_pool.json 2>gpurun_out/bench_pool.err; echo "bench rc=$?"
+python -c "
+import json; d=json.load(open('gpurun_out/bench_pool.json')); print(d['value'], d['kernels']['refine_ms'], d['front_end']['fused_ms'], d['front_end']['torch_glue_ms'], d['e2e']['value'], d['frame_pipeline']['ms_per_frame'])"
