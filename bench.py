@@ -592,6 +592,8 @@ def cpu_baseline_matching(M, steps=1, warmup=0, seed=0):
     import m3r_oracle as oracle
 
     oracle.build()
+    # all host threads, whatever the launcher put in OMP_NUM_THREADS (torchrun sets it to 1)
+    oracle.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
     sets = make_match_sets("cpu", 1, seed0=seed)
     for _ in range(warmup):
         cpu_match_pass(oracle, sets[0], M)
@@ -608,6 +610,7 @@ def cpu_baseline_gn(D, num_kf=8, iters=1):
     import m3r_oracle as oracle
     import synth
 
+    oracle.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
     g = synth.make_graph(num_kf, H, W, seed=0, device="cpu")
     P = oracle.make_params("rays", sigma_ray=D["sigma_ray"], sigma_dist=D["sigma_dist"],
                            C_thresh=D["C_thresh"], Q_thresh=D["Q_thresh"])
