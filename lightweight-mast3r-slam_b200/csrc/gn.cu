@@ -242,7 +242,14 @@ struct Residual<M3R_GN_CALIB> {
 //     bytes per surviving point instead of 13 per point, and carries no validity logic.
 // Order within a segment is preserved and segments are summed in a fixed order, so results
 // stay bitwise reproducible.
-constexpr int kAccThreads = 256;
+#ifndef M3R_ACC_THREADS
+#define M3R_ACC_THREADS 256
+#endif
+#ifndef M3R_ACC_CTAS
+#define M3R_ACC_CTAS 2
+#endif
+constexpr int kAccThreads = M3R_ACC_THREADS;  // accumulation kernel: threads per CTA ...
+constexpr int kAccCtasPerSM = M3R_ACC_CTAS;    // ... and resident CTAs per SM (register budget)
 constexpr int kAccWarps = kAccThreads / 32;
 constexpr int kSeg = 2048;                  // points per warp segment
 constexpr int kChunk = kSeg * kAccWarps;    // points per work item (one CTA pass)
@@ -376,7 +383,7 @@ __device__ __forceinline__ void cp_async16_ca(void *smem_dst, const void *gsrc) 
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kAccThreads, 2) gn_accumulate_kernel(const AccArgs A) {
+__global__ void __launch_bounds__(kAccThreads, kAccCtasPerSM) gn_accumulate_kernel(const AccArgs A) {
   if (A.flags[0]) return;  // converged earlier: nothing to do
   extern __shared__ __align__(16) unsigned char acc_smem_raw[];
   __shared__ double red[kAccWarps][kNAcc];
@@ -1149,7 +1156,7 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
     a.flags = ws->flags;
     a.n = n, a.edge_begin = prob->edge_begin, a.num_shard_edges = ES, a.chunks_per_edge = chunks;
     a.P_ = make_params(prob);
-    const size_t cap = static_cast<size_t>(kNumSMs) * 2;
+    const size_t cap = static_cast<size_t>(kNumSMs) * kAccCtasPerSM;
     const int grid = static_cast<int>(items < cap ? items : cap);
     static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
     bool &attr_set = attr_set_dev[ws->device & 63];
