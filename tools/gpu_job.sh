@@ -1,4 +1,4 @@
-for v in "" tools/_var_acc_192_3.so tools/_var_acc_288_2.so tools/_var_acc_128_4.so tools/_var_acc_160_3.so tools/_var_acc_128_5.so tools/_var_acc_160_4.so tools/_var_acc_96_6.so; do
-  if [ -n "$v" ]; then export M3R_B200_LIB=$PWD/$v; else unset M3R_B200_LIB; fi
-  KINDS=rays,calib timeout 300 python tools/gn_var.py 2>&1 | tail -2
+timeout 900 python -m pytest tests/test_matching_gpu.py tests/test_front_gpu.py -m gpu -q -x > gpurun_out/pytest_match.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_match.log
+for g in 0 148 296 472 768; do
+  echo "NSPLIT=$g"; M3R_REFINE_NSPLIT=$g timeout 300 python tools/refine_var.py 2>&1 | tail -1
 done
