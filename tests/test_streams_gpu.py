@@ -77,3 +77,34 @@ def test_two_streams_interleaved(backends):
                 assert torch.equal(r[0], Tw0) and torch.equal(r[1], Tk0)
             else:
                 assert torch.equal(r[0], idx0) and torch.equal(r[1], valid0)
+
+
+def test_matching_under_cuda_graph_capture(backends):
+    """iter_proj -> .long() -> refine_matches captured into a CUDA graph and replayed: the refine
+    plan scratch is a stream-ordered allocation (a graph memory node under capture), nothing in
+    the two calls synchronises or allocates outside the stream.  Replays equal the eager result."""
+    m = synth.make_match_inputs(96, 128, seed=4, device="cuda")
+    rays, pts, p0 = synth.prep_for_iter_proj(m["X11"], m["X21"])
+    D11 = m["D11"].half().contiguous()
+    D21 = m["D21"].view(1, 96 * 128, -1).half().contiguous()
+
+    def run():
+        p, conv = backends.iter_proj(rays, pts, p0, M["max_iter"], M["lambda_init"], M["convergence_thresh"])
+        (p1n,) = backends.refine_matches(D11, D21, p.long(), M["radius"], M["dilation_max"])
+        return p, conv, p1n
+
+    eager = [x.clone() for x in run()]
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):  # warm-up on the capture stream, as torch asks
+        run()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = run()
+    for _ in range(3):
+        for o in out:
+            o.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b) for a, b in zip(eager, out))
