@@ -1,1 +1,4 @@
-timeout 900 python -m pytest tests/test_streams_gpu.py -m gpu -q -x 2>&1 | tail -15
+set -x
+( time timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1 ) 2> gpurun_out/pytest_gpu.time; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
+bash tools/gpu_round1.sh
