@@ -147,9 +147,9 @@ def test_refine_kernels_agree(backends, oracle, h, w, b, kind):
 
 
 def test_refine_many_tiles(backends):
-    """More tiles than the plan pass orders (4096): the unplanned grid of tiles; and tile counts
-    that end inside a thread's group of 16 flags."""
-    for h, w, b in [(640, 656, 3), (16, 272, 1), (48, 528, 1)]:  # 4920, 17 and 99 tiles
+    """More tiles than the plan pass orders: the unplanned grid of tiles; and tile counts that end
+    inside a thread's group of 16 flags."""
+    for h, w, b in [(640, 656, 3), (16, 272, 1), (48, 528, 1), (384, 512, 3)]:  # 4920, 17, 99 and 2304 tiles
         g = torch.Generator().manual_seed(h + w)
         D11 = torch.randn(b, h, w, 24, generator=g).half().cuda()
         D21 = torch.randn(b, h * w, 24, generator=g).half().cuda()
