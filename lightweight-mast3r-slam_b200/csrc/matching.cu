@@ -604,6 +604,9 @@ __global__ void __launch_bounds__(kRtThreads)
                        unsigned char *__restrict__ heavy, int h, int w, int dilation_max, int tiles_x,
                        int tiles_y) {
   // one CTA per tile, one query per thread: every load of the pass is in flight at once
+  // (the main kernel is launched with programmatic stream serialisation: its CTAs may be set up
+  // while this grid runs; they wait for this grid's results at their griddepcontrol.wait)
+  asm volatile("griddepcontrol.launch_dependents;");
   __shared__ int red[5];
   const int t = blockIdx.x, tid = threadIdx.x;
   const int per_img = tiles_x * tiles_y;
@@ -658,6 +661,7 @@ __global__ void __launch_bounds__(kRtThreads, 2)
     // this CTA's tile: the blockIdx.x-th entry of (heavy tiles in index order, then the others).
     // Every thread owns 16 consecutive flags; a block-wide prefix sum of the heavy counts finds
     // the owner of the wanted rank.
+    asm volatile("griddepcontrol.wait;" ::: "memory");  // the plan pass has finished and is visible
     int *scan = red;  // [0..7] warp totals, [8] the tile
     const int first_id = tid * 16;
     const int nvalid = min(max(ntiles - first_id, 0), 16);
@@ -1019,9 +1023,17 @@ static int launch_refine_tiled(const __half *D11, const __half *D21, const long 
     const int nt = static_cast<int>(ntiles);
     refine_plan_kernel<<<nt, kRtThreads, 0, s>>>(p1, plan, heavy, h, w, dilation_max, tiles_x, tiles_y);
     g_launch_count.fetch_add(1, std::memory_order_relaxed);
-    refine_f16_tiled_kernel<true><<<nt, kRtThreads, kRtSmemBytes, s>>>(
-        D11, D21, p1, p1_new, lin_out, h, w, dilation_max, plan, heavy, tiles_x, tiles_y, nt);
-    const cudaError_t e = cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(nt), cfg.blockDim = dim3(kRtThreads), cfg.dynamicSmemBytes = kRtSmemBytes, cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    const int4 *plan_c = plan;
+    const unsigned char *heavy_c = heavy;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, refine_f16_tiled_kernel<true>, D11, D21, p1, p1_new, lin_out, h, w,
+                                       dilation_max, plan_c, heavy_c, tiles_x, tiles_y, nt);
+    if (e == cudaSuccess) e = cudaGetLastError();
     const cudaError_t ef = cudaFreeAsync(scratch, s);
     g_launch_count.fetch_add(1, std::memory_order_relaxed);
     if (e != cudaSuccess) return cuda_fail(e, "refine_f16_tiled_kernel<planned>");
