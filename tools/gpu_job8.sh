@@ -1,7 +1,9 @@
 set -x
 N=${NGPU:-8}
 nvidia-smi -L | wc -l
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2961$N tools/gn_scale.py rays:64 calib:64 points:256 > gpurun_out/gn_scale_n$N.jsonl 2> gpurun_out/gn_scale_n$N.err; echo "scale$N rc=$?"
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N --steps 50 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench$N rc=$?"
-cat gpurun_out/gn_scale_n$N.jsonl
-tail -2 gpurun_out/gn_scale_n$N.err
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N --steps 50 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench$N rc=$?"
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2952$N bench.py --impl reference --gpus $N --steps 2 --warmup 1 > gpurun_out/bench_ref_n$N.json 2> gpurun_out/bench_ref_n$N.err; echo "benchref$N rc=$?"
+python -c "
+import json; d=json.load(open('gpurun_out/bench_n$N.json')); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value'], d['gn']['value'], d['gn'].get('exchange'), d['gn'].get('nccl_variant'))
+r=json.load(open('gpurun_out/bench_ref_n$N.json')); print(r['value'], r['cpu_baseline']['cores'])"
+tail -3 gpurun_out/bench_n$N.err
