@@ -893,6 +893,92 @@ __global__ void __launch_bounds__(kSolveThreads)
   finish_step<kSolveThreads>(t, fail, D, xbuf, Twc, dx, num_poses, delta_thresh, flags);
 }
 
+// ----------------------------------------------------------------------------------------
+// small systems: the whole solve in the shared memory of one CTA
+// ----------------------------------------------------------------------------------------
+// Up to kSmallMaxD unknowns (8 keyframes: the graph of a SLAM run's first seconds) the cooperative
+// kernel is all fixed cost (launch, one grid barrier per 32-column panel, the substitutions): 21 us
+// at D = 21, 46 us at D = 49.  This kernel takes 17 and 36 us there; at D = 63 the two are equal
+// (50 / 48 us) and at D = 105 it takes 105 us against 75 (a plain column algorithm: two barriers
+// and one shared-memory round trip per column), hence the limit.  Here the lower triangle is
+// copied once into shared memory as packed rows with the right-hand side as row D, so that the
+// forward substitution is part of the factorisation (row D ends up as y = L^-1 b); a right-looking
+// column Cholesky follows (every thread recomputes the pivot's root and reciprocal instead of
+// waiting for one thread's: two barriers per column), then the backward substitution on one warp
+// and the common finish (dx = -x, retraction, stop test).  fp64 throughout, like the Eigen LLT of
+// the reference (gn_kernels.cu:132-150); a non-positive or non-finite pivot gives dx = 0.
+constexpr int kSmallThreads = 512;
+constexpr int kSmallMaxD = 49;  // 7 * 7: where it was measured to beat the cooperative kernel
+
+__host__ __device__ constexpr size_t small_smem_doubles(int D) {
+  return static_cast<size_t>(D + 1) * (D + 2) / 2 + 3 * static_cast<size_t>(D) + 8;
+}
+
+__global__ void __launch_bounds__(kSmallThreads)
+    gn_chol_solve_small_kernel(const double *__restrict__ sys, int D, float *__restrict__ Twc,
+                               float *__restrict__ dx, int num_poses, float delta_thresh,
+                               int *__restrict__ flags) {
+  if (flags[0]) return;
+  extern __shared__ double small_sm[];
+  double *A = small_sm;                                          // packed rows 0..D, row i at i(i+1)/2
+  double *col = A + static_cast<size_t>(D + 1) * (D + 2) / 2;    // current column, scaled  [D+1]
+  double *invd = col + D + 1;                                    // 1 / L_jj                [D]
+  double *xv = invd + D;                                         // solution               [D]
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  constexpr int NW = kSmallThreads / 32;
+  auto row = [&](int i) { return A + static_cast<size_t>(i) * (i + 1) / 2; };
+
+  // rows of the lower triangle (the assembled system is block-lower: every element with
+  // column <= row is meaningful), then the right-hand side as row D
+  for (int i = warp; i <= D; i += NW) {
+    const double *src = i < D ? sys + static_cast<size_t>(i) * D : sys + static_cast<size_t>(D) * D;
+    const int len = i < D ? i + 1 : D;
+    double *dst = row(i);
+    for (int j = lane; j < len; j += 32) dst[j] = src[j];
+  }
+  __syncthreads();
+
+  bool fail = flags[2] != 0;
+  for (int j = 0; j < D && !fail; j++) {
+    const double d = row(j)[j];  // same value in every thread: the decision below is uniform
+    if (!(d > 0.0) || !isfinite(d)) {
+      fail = true;
+      break;
+    }
+    const double inv = rsqrt(d);
+    for (int i = j + 1 + t; i <= D; i += kSmallThreads) {
+      const double v = row(i)[j] * inv;
+      row(i)[j] = v;
+      col[i] = v;
+    }
+    if (t == 0) invd[j] = inv;
+    __syncthreads();
+    // trailing update A[r][c] -= L[r][j] L[c][j] for j < c <= min(r, D-1), j < r <= D
+    for (int r = j + 1 + warp; r <= D; r += NW) {
+      const double lr = col[r];
+      double *ar = row(r);
+      const int cmax = r < D ? r : D - 1;
+      for (int c = j + 1 + lane; c <= cmax; c += 32) ar[c] -= lr * col[c];
+    }
+    __syncthreads();
+  }
+
+  if (!fail && warp == 0) {
+    // backward: L^T x = y, y = row D; x_j = y_j / L_jj = y_j * inv_j^... (L_jj = d_j * inv_j, so
+    // 1 / L_jj = inv_j of the already updated pivot d_j: invd holds rsqrt(d_j) = 1 / L_jj)
+    double *y = row(D);
+    for (int j = D - 1; j >= 0; j--) {
+      const double xj = y[j] * invd[j];
+      const double *lj = row(j);
+      for (int i = lane; i < j; i += 32) y[i] -= lj[i] * xj;
+      if (lane == 0) xv[j] = xj;
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  finish_step<kSmallThreads>(t, fail, D, xv, Twc, dx, num_poses, delta_thresh, flags);
+}
+
 #include "gn_chol_coop.cuh"
 #include "gn_chol_cluster.cuh"
 
@@ -1209,9 +1295,24 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     const char *e = getenv("M3R_GN_SOLVER");
     if (e && strcmp(e, "multi") == 0) return 2;
     if (e && strcmp(e, "cluster") == 0) return 0;
+    if (e && strcmp(e, "coop") == 0) return 3;  // the cooperative kernel at every size
     return 1;
   }();
   const bool use_multi = solver_choice == 2;
+  if (solver_choice == 1 && D <= kSmallMaxD) {
+    // small system: one CTA, matrix in shared memory
+    const size_t smem = small_smem_doubles(D) * sizeof(double);
+    static bool small_attr_dev[64] = {false};
+    if (!small_attr_dev[ws->device & 63]) {
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_chol_solve_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        static_cast<int>(small_smem_doubles(kSmallMaxD) * sizeof(double))));
+      small_attr_dev[ws->device & 63] = true;
+    }
+    gn_chol_solve_small_kernel<<<1, kSmallThreads, smem, s>>>(system, D, prob->Twc, dx, prob->num_poses,
+                                                              delta_thresh, ws->flags);
+    M3R_LAUNCH_CHECK("gn_chol_solve_small_kernel");
+    return M3R_OK;
+  }
   if (solver_choice == 0 && D <= kClMaxD) {
     // one 8-CTA cluster, matrix resident in distributed shared memory
     if ((rc = ws->xbuf.reserve(static_cast<size_t>(kClMaxD)))) return rc;

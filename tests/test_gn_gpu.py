@@ -102,10 +102,11 @@ def test_first_step_and_final_poses_vs_oracle(backends, oracle, kind, N, h, w, s
     assert e_dx < TOL and e_T1 < TOL and e_T10 < TOL
 
 
-@pytest.mark.parametrize("N", [64, 65, 70])
+@pytest.mark.parametrize("N", [2, 3, 8, 9, 64, 65, 70])
 def test_solver_by_system_size(backends, oracle, N):
-    """D = 7(N-1) = 441, 448, 483 (14, 14 and 16 panels of the blocked Cholesky): same answers
-    as the oracle's Eigen-style fp64 solve."""
+    """D = 7(N-1) = 7, 14, 49 (single-CTA shared-memory solver, up to its limit), 56 (first size of
+    the cooperative kernel), 441, 448, 483 (14, 14 and 16 panels of the blocked Cholesky): same
+    answers as the oracle's Eigen-style fp64 solve."""
     e_dx, e_T = _solver_check(backends, oracle, N)
     assert e_dx < TOL and e_T < TOL
 
@@ -122,10 +123,12 @@ def _solver_check(backends, oracle, N):
     return e_dx, e_T
 
 
-@pytest.mark.parametrize("solver", ["cluster", "multi"])
+@pytest.mark.parametrize("solver", ["cluster", "multi", "coop"])
 def test_alternative_solvers(solver):
     """The opt-in solvers (M3R_GN_SOLVER is read once per process): the 8-CTA cluster Cholesky
-    with the matrix in distributed shared memory, and the multi-launch blocked Cholesky."""
+    with the matrix in distributed shared memory, the multi-launch blocked Cholesky, and the
+    cooperative kernel forced at every size (by default systems of up to 49 unknowns go to the
+    single-CTA shared-memory solver)."""
     import subprocess
     import sys
 
