@@ -643,6 +643,7 @@ __global__ void __launch_bounds__(64)
 // ----------------------------------------------------------------------------------------
 constexpr int kPB = 32;  // panel width
 
+#ifdef M3R_TEST_VARIANTS  // the multi-launch solver: a test-only variant (tests/_variants build)
 // Factor the kPB x kPB diagonal block at k0 in shared memory (every CTA does it redundantly,
 // it is 11k flops), then solve this CTA's 64 rows of the panel: L21 = A21 L11^-T.
 // CTA 0 also stores L11.
@@ -753,6 +754,8 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+#endif  // M3R_TEST_VARIANTS
+
 // ----------------------------------------------------------------------------------------
 // triangular solves, dx = -x, retraction, stop test (one CTA)
 // ----------------------------------------------------------------------------------------
@@ -817,6 +820,7 @@ __device__ void finish_step(const int t, const bool fail, const int D, const dou
   }
 }
 
+#ifdef M3R_TEST_VARIANTS
 constexpr int kSolveThreads = 512;
 
 __global__ void __launch_bounds__(kSolveThreads)
@@ -892,6 +896,8 @@ __global__ void __launch_bounds__(kSolveThreads)
 
   finish_step<kSolveThreads>(t, fail, D, xbuf, Twc, dx, num_poses, delta_thresh, flags);
 }
+
+#endif  // M3R_TEST_VARIANTS
 
 // ----------------------------------------------------------------------------------------
 // small systems: the whole solve in the shared memory of one CTA
@@ -980,14 +986,109 @@ __global__ void __launch_bounds__(kSmallThreads)
 }
 
 #include "gn_chol_coop.cuh"
+#ifdef M3R_TEST_VARIANTS
 #include "gn_chol_cluster.cuh"
+#endif
 
 // ----------------------------------------------------------------------------------------
 // keyframe id -> packed pose index (sorted-unique rank), no host sync
 // ----------------------------------------------------------------------------------------
+// get_unique_kf_idx + create_inds (gn_kernels.cu:161-170: unique(cat(ii, jj)) sorted, then
+// searchsorted) without a sort: keyframe ids index the shared keyframe buffer (at most 512 slots,
+// frame.py:221), so one CTA marks the ids that occur in a bitmap in shared memory, an exclusive
+// prefix sum over the words' popcounts gives the number of distinct ids below each word, and
+//   rank(id) = prefix[id / 32] + popc(word[id / 32] & ((1 << id % 32) - 1)).
+// O(E + kRemapMaxId / 32) instead of the O(E^2) pair of kernels this replaces (93 us at E = 492).
+// Ids outside [0, kRemapMaxId) take the general kernels below.  flags[3] = kGnErrBadPoseCount when
+// the graph holds more distinct ids than the caller's num_poses (the reference would index out of
+// bounds; here the rank is clamped for memory safety and the error is reported by
+// m3r_gn_iterations_done).
+constexpr int kGnErrExchangeTimeout = 1;  // flags[3]
+constexpr int kGnErrBadPoseCount = 2;
+constexpr int kRemapMaxId = 1 << 16;
+constexpr int kRemapWords = kRemapMaxId / 32;
+constexpr int kRemapThreads = 1024;
+
+__device__ __forceinline__ void gn_reset_flags(int *flags) {
+  flags[0] = 0;  // done
+  flags[1] = 0;  // iterations executed
+  flags[2] = 0;  // factorisation failed
+  flags[3] = 0;  // error code
+}
+
+__global__ void __launch_bounds__(kRemapThreads)
+    gn_remap_kernel(const long long *__restrict__ ii, const long long *__restrict__ jj, int E,
+                    int num_poses, int *__restrict__ pose_i, int *__restrict__ pose_j,
+                    int *__restrict__ flags, int *__restrict__ fallback) {
+  __shared__ unsigned bits[kRemapWords];
+  __shared__ int prefix[kRemapWords];
+  __shared__ int warp_tot[kRemapThreads / 32];
+  __shared__ int out_of_range;
+  const int t = threadIdx.x;
+  if (t == 0) {
+    gn_reset_flags(flags);
+    out_of_range = 0;
+  }
+  for (int k = t; k < kRemapWords; k += kRemapThreads) bits[k] = 0u;
+  __syncthreads();
+  for (int k = t; k < 2 * E; k += kRemapThreads) {
+    const long long v = (k < E) ? ii[k] : jj[k - E];
+    if (v < 0 || v >= kRemapMaxId) out_of_range = 1;
+    else atomicOr(&bits[v >> 5], 1u << (v & 31));
+  }
+  __syncthreads();
+  if (out_of_range) {  // uniform
+    if (t == 0) *fallback = 1;
+    return;
+  }
+  if (t == 0) *fallback = 0;
+  // exclusive scan of popc(bits[]) : kRemapWords / kRemapThreads consecutive words per thread
+  constexpr int kPer = kRemapWords / kRemapThreads;
+  int loc[kPer], sum = 0;
+#pragma unroll
+  for (int u = 0; u < kPer; u++) {
+    loc[u] = sum;
+    sum += __popc(bits[t * kPer + u]);
+  }
+  int incl = sum;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, off);
+    if ((t & 31) >= off) incl += o;
+  }
+  if ((t & 31) == 31) warp_tot[t >> 5] = incl;
+  __syncthreads();
+  if (t < 32) {
+    int w = warp_tot[t];
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, w, off);
+      if (t >= off) w += o;
+    }
+    warp_tot[t] = w;  // inclusive over warps
+  }
+  __syncthreads();
+  const int base = incl - sum + ((t >> 5) > 0 ? warp_tot[(t >> 5) - 1] : 0);
+#pragma unroll
+  for (int u = 0; u < kPer; u++) prefix[t * kPer + u] = base + loc[u];
+  __syncthreads();
+  if (t == 0 && warp_tot[kRemapThreads / 32 - 1] > num_poses) flags[3] = kGnErrBadPoseCount;
+  for (int k = t; k < 2 * E; k += kRemapThreads) {
+    const long long v = (k < E) ? ii[k] : jj[k - E];
+    int rank = prefix[v >> 5] + __popc(bits[v >> 5] & ((1u << (v & 31)) - 1u));
+    rank = min(rank, num_poses - 1);  // memory safety when the caller's N is inconsistent
+    if (k < E) pose_i[k] = rank;
+    else pose_j[k - E] = rank;
+  }
+}
+
+// general ids (any int64): first occurrences, then rank = number of smaller first occurrences.
+// O(E^2); only runs when gn_remap_kernel met an id outside [0, kRemapMaxId).
 __global__ void gn_first_occurrence_kernel(const long long *__restrict__ ii,
                                            const long long *__restrict__ jj, int E,
-                                           unsigned char *__restrict__ first) {
+                                           unsigned char *__restrict__ first,
+                                           const int *__restrict__ fallback) {
+  if (*fallback == 0) return;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= 2 * E) return;
   const long long v = (k < E) ? ii[k] : jj[k - E];
@@ -1005,13 +1106,9 @@ __global__ void gn_first_occurrence_kernel(const long long *__restrict__ ii,
 __global__ void gn_rank_kernel(const long long *__restrict__ ii, const long long *__restrict__ jj,
                                int E, const unsigned char *__restrict__ first, int num_poses,
                                int *__restrict__ pose_i, int *__restrict__ pose_j,
-                               int *__restrict__ flags) {
+                               int *__restrict__ flags, const int *__restrict__ fallback) {
+  if (*fallback == 0) return;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k == 0) {
-    flags[0] = 0;  // done
-    flags[1] = 0;  // iterations executed
-    flags[2] = 0;  // factorisation failed
-  }
   if (k >= 2 * E) return;
   const long long v = (k < E) ? ii[k] : jj[k - E];
   int rank = 0;
@@ -1019,7 +1116,8 @@ __global__ void gn_rank_kernel(const long long *__restrict__ ii, const long long
     const long long o = (m < E) ? ii[m] : jj[m - E];
     rank += (first[m] && o < v) ? 1 : 0;
   }
-  rank = min(rank, num_poses - 1);  // memory safety if the caller's N is inconsistent
+  if (rank >= num_poses) flags[3] = kGnErrBadPoseCount;
+  rank = min(rank, num_poses - 1);
   if (k < E) pose_i[k] = rank;
   else pose_j[k - E] = rank;
 }
@@ -1070,7 +1168,8 @@ struct m3r_gn_workspace {
   DevBuf<double> system;          // D*D + D (single-GPU entry points)
   DevBuf<double> ldiag;           // factored diagonal blocks of the Cholesky
   DevBuf<double> xbuf;            // [D]
-  int *flags = nullptr;           // [0] done, [1] iterations, [2] factorisation failed
+  int *flags = nullptr;           // [0] done, [1] iterations, [2] factorisation failed, [3] error code
+                                  // (kGnErr*), [4] id remap took the general path
   int begun_edges = -1;
   int begun_shard_begin = -1, begun_shard_end = -1, begun_points = -1;
 };
@@ -1081,8 +1180,8 @@ extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
   M3R_REQUIRE(out != nullptr, "gn_workspace_create: null out pointer");
   m3r_gn_workspace *ws = new m3r_gn_workspace();
   cudaError_t e = cudaGetDevice(&ws->device);
-  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&ws->flags), 4 * sizeof(int));
-  if (e == cudaSuccess) e = cudaMemset(ws->flags, 0, 4 * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&ws->flags), 8 * sizeof(int));
+  if (e == cudaSuccess) e = cudaMemset(ws->flags, 0, 8 * sizeof(int));
   if (e != cudaSuccess) {
     delete ws;
     return cuda_fail(e, "gn_workspace_create");
@@ -1139,16 +1238,19 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
   ws->begun_edges = E;
   const int M = 2 * E;
   const int blocks = (M + 255) / 256;
-  if (blocks > 0) {
-    gn_first_occurrence_kernel<<<blocks, 256, 0, s>>>(
-        reinterpret_cast<const long long *>(prob->ii), reinterpret_cast<const long long *>(prob->jj),
-        E, ws->first.p);
+  const long long *ii_p = reinterpret_cast<const long long *>(prob->ii);
+  const long long *jj_p = reinterpret_cast<const long long *>(prob->jj);
+  int *fallback = ws->flags + 4;
+  gn_remap_kernel<<<1, kRemapThreads, 0, s>>>(ii_p, jj_p, E, prob->num_poses, ws->pose_i.p, ws->pose_j.p,
+                                              ws->flags, fallback);
+  M3R_LAUNCH_CHECK("gn_remap_kernel");
+  if (blocks > 0) {  // both return at once unless an id fell outside the bitmap
+    gn_first_occurrence_kernel<<<blocks, 256, 0, s>>>(ii_p, jj_p, E, ws->first.p, fallback);
     M3R_LAUNCH_CHECK("gn_first_occurrence_kernel");
+    gn_rank_kernel<<<blocks, 256, 0, s>>>(ii_p, jj_p, E, ws->first.p, prob->num_poses, ws->pose_i.p,
+                                          ws->pose_j.p, ws->flags, fallback);
+    M3R_LAUNCH_CHECK("gn_rank_kernel");
   }
-  gn_rank_kernel<<<blocks > 0 ? blocks : 1, 256, 0, s>>>(
-      reinterpret_cast<const long long *>(prob->ii), reinterpret_cast<const long long *>(prob->jj), E,
-      ws->first.p, prob->num_poses, ws->pose_i.p, ws->pose_j.p, ws->flags);
-  M3R_LAUNCH_CHECK("gn_rank_kernel");
 
   // per-call preparation: packed keyframes, compacted match lists of this shard
   const int n = prob->num_points;
@@ -1289,8 +1391,10 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
   const int D = 7 * (prob->num_poses - 1);
   if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
   if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride))) return rc;
-  // M3R_GN_SOLVER = coop (default) | cluster (D <= 448 only; measured slower: 430 vs 340 us at
-  // D = 441, profiles/r1_d_cluster_solver_phases.txt) | multi   (benchmarks, tests)
+#ifdef M3R_TEST_VARIANTS
+  // variants build only (tests/_variants): M3R_GN_SOLVER = cluster (D <= 448; measured slower: 430
+  // vs 340 us at D = 441, profiles/r1_d_cluster_solver_phases.txt) | multi (one launch per panel
+  // phase) | coop (the cooperative kernel at every size).  The product library has no switch.
   static const int solver_choice = [] {
     const char *e = getenv("M3R_GN_SOLVER");
     if (e && strcmp(e, "multi") == 0) return 2;
@@ -1298,7 +1402,9 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     if (e && strcmp(e, "coop") == 0) return 3;  // the cooperative kernel at every size
     return 1;
   }();
-  const bool use_multi = solver_choice == 2;
+#else
+  constexpr int solver_choice = 1;
+#endif
   if (solver_choice == 1 && D <= kSmallMaxD) {
     // small system: one CTA, matrix in shared memory
     const size_t smem = small_smem_doubles(D) * sizeof(double);
@@ -1313,6 +1419,7 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     M3R_LAUNCH_CHECK("gn_chol_solve_small_kernel");
     return M3R_OK;
   }
+#ifdef M3R_TEST_VARIANTS
   if (solver_choice == 0 && D <= kClMaxD) {
     // one 8-CTA cluster, matrix resident in distributed shared memory
     if ((rc = ws->xbuf.reserve(static_cast<size_t>(kClMaxD)))) return rc;
@@ -1329,7 +1436,11 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     M3R_LAUNCH_CHECK("gn_chol_solve_cluster_kernel");
     return M3R_OK;
   }
-  if (!use_multi) {
+  const bool use_multi = solver_choice == 2;
+  if (!use_multi)
+#endif
+  {
+
     // one cooperative launch: Cholesky + substitutions + retraction + stop test
     static bool coop_attr_dev[64] = {false};
     if (!coop_attr_dev[ws->device & 63]) {
@@ -1337,10 +1448,11 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kCoopSmemBytes));
       coop_attr_dev[ws->device & 63] = true;
     }
-    static int max_coresident = 0;
+    static int max_coresident_dev[64] = {0};  // per device (SM counts differ under MIG / mixed parts)
+    int &max_coresident = max_coresident_dev[ws->device & 63];
     if (max_coresident == 0) {
-      int dev = 0, sms = 0, per_sm = 0;
-      M3R_CUDA_TRY(cudaGetDevice(&dev));
+      int sms = 0, per_sm = 0;
+      const int dev = ws->device;
       M3R_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
       M3R_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_chol_solve_coop_kernel,
                                                                 kCoopThreads, kCoopSmemBytes));
@@ -1367,6 +1479,7 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
     g_launch_count.fetch_add(1, std::memory_order_relaxed);
     return M3R_OK;
   }
+#ifdef M3R_TEST_VARIANTS
   for (int k0 = 0; k0 < D; k0 += kPB) {
     const int rows_below = D - k0 - kPB;
     const int pblocks = rows_below > 0 ? (rows_below + 63) / 64 : 1;
@@ -1383,17 +1496,20 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
                                                       delta_thresh, ws->flags);
   M3R_LAUNCH_CHECK("gn_solve_retract_kernel");
   return M3R_OK;
+#endif
 }
 
-// debug: cumulative per-phase cycle counts of the cooperative solver (CTA 0), then reset
-extern "C" int m3r_debug_coop_profile(long long *out8) {  // 16 entries
+#ifdef M3R_COOP_PROF
+// experiments (tools/kbench.py): cumulative per-phase cycle counts of the cooperative solver
+extern "C" int m3r_debug_coop_profile(long long *out16) {
   long long zero[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   M3R_CUDA_TRY(cudaDeviceSynchronize());
-  M3R_CUDA_TRY(cudaMemcpyFromSymbol(out8, g_coop_prof, sizeof(zero)));
+  M3R_CUDA_TRY(cudaMemcpyFromSymbol(out16, g_coop_prof, sizeof(zero)));
   M3R_CUDA_TRY(cudaMemcpyToSymbol(g_coop_prof, zero, sizeof(zero)));
   return M3R_OK;
 }
-
+#endif
+#ifdef M3R_TEST_VARIANTS
 extern "C" int m3r_debug_cluster_profile(long long *out9) {
   long long zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   M3R_CUDA_TRY(cudaDeviceSynchronize());
@@ -1401,6 +1517,7 @@ extern "C" int m3r_debug_cluster_profile(long long *out9) {
   M3R_CUDA_TRY(cudaMemcpyToSymbol(g_cl_prof, zero, sizeof(zero)));
   return M3R_OK;
 }
+#endif
 
 extern "C" int m3r_gn_edge_blocks(m3r_gn_workspace *ws, const double **Hjj, const double **gj) {
   M3R_REQUIRE(ws && Hjj && gj, "gn_edge_blocks: null pointer");
@@ -1416,9 +1533,13 @@ extern "C" int m3r_gn_iterations_done(m3r_gn_workspace *ws, void *stream, int *i
   M3R_CUDA_TRY(cudaMemcpyAsync(host, ws->flags, sizeof(host), cudaMemcpyDeviceToHost, s));
   M3R_CUDA_TRY(cudaStreamSynchronize(s));
   *iters = host[1];
-  if (host[3] != 0) {
-    set_error("gn: a multi-GPU exchange timed out waiting for a peer");
+  if (host[3] == kGnErrExchangeTimeout) {
+    set_error("gn: a multi-GPU exchange timed out waiting for a peer (the solve was stopped)");
     return M3R_ERR_CUDA;
+  }
+  if (host[3] == kGnErrBadPoseCount) {
+    set_error("gn: ii/jj hold more distinct keyframe ids than num_poses");
+    return M3R_ERR_INVALID_ARGUMENT;
   }
   return M3R_OK;
 }

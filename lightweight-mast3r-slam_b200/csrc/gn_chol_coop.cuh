@@ -21,6 +21,9 @@ namespace cg = ::cooperative_groups;  // <cooperative_groups.h> is included by g
 
 // cycles CTA 0 spent in: [0] phase A, [1] barrier 1, [2] phase B, [3] barrier 2, [4] backward
 // substitution, [5] finish_step; [6] launches.  Read by m3r_debug_coop_profile (tools/).
+// The clock64() reads are compiled in only with -DM3R_COOP_PROF (tools/, experiments): the product
+// kernel carries none of them.
+#ifdef M3R_COOP_PROF
 __device__ long long g_coop_prof[16];  // [8..13]: phase A split of CTA 0, see COOP_ATICK
 #define COOP_TICK(slot)                                   \
   do {                                                    \
@@ -52,6 +55,11 @@ __device__ long long g_coop_prof[16];  // [8..13]: phase A split of CTA 0, see C
       aprof_t = now_;                                     \
     }                                                     \
   } while (0)
+#else
+#define COOP_TICK(slot) do { } while (0)
+#define COOP_TTICK(slot) do { } while (0)
+#define COOP_ATICK(slot) do { } while (0)
+#endif
 
 constexpr int kCoopThreads = 256;
 constexpr int kLdStride = kPB * (kPB + 1);  // per panel in `ldiag`: L11 (kPB x kPB) + 1/diag (kPB)
@@ -210,12 +218,14 @@ __global__ void __launch_bounds__(kCoopThreads)
   double *A = sys;
   double *rhs = sys + static_cast<size_t>(D) * D;
   if (t == 0) bad = 0;
+#ifdef M3R_COOP_PROF
   long long prof_acc[6] = {0, 0, 0, 0, 0, 0};
   long long prof_t = clock64();
   long long aprof[6] = {0, 0, 0, 0, 0, 0};
   long long tprof[4] = {0, 0, 0, 0};  // thread 32 (first TRSM warp) of CTA 0, see COOP_TTICK
   long long tprof_t = 0;
   long long aprof_t = 0;
+#endif
   __syncthreads();
   // warp roles in phase A: 0 = POTRF (alone on its scheduler: warp 4 idles), 1,2,3,6 = the
   // CTA's 128 panel rows (look-ahead update, TRSM, rhs), 5 = forward-substitution chain y_k
@@ -234,7 +244,9 @@ __global__ void __launch_bounds__(kCoopThreads)
     const int kp = k0 - kPB;
     // ---------------- phase A (panel CTAs)
     for (int rc = blockIdx.x; rc < row_ctas; rc += gridDim.x) {
+#ifdef M3R_COOP_PROF
       if (blockIdx.x == 0 && t == 0) aprof_t = clock64();
+#endif
       const int row0 = k0 + pb + rc * kTrsmRows;
       const int nrows = max(0, min(kTrsmRows, D - row0));
       // named barrier 1 ("L11 ready"): warp 0 arrives; the TRSM warps, the y_k warp and, on the
@@ -255,7 +267,9 @@ __global__ void __launch_bounds__(kCoopThreads)
       if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
       __syncthreads();
       COOP_ATICK(8);
+#ifdef M3R_COOP_PROF
       if (blockIdx.x == 0 && t == 32) tprof_t = clock64();
+#endif
       // the row loads are shared with the two warps that have nothing else to do (3 and 6): one
       // batch of 32 independent loads per thread instead of eight dependent batches
       const bool load_warp = trsm_warp || warp == 3 || warp == 6;
@@ -558,6 +572,7 @@ __global__ void __launch_bounds__(kCoopThreads)
   COOP_TICK(4);
   finish_step<kCoopThreads>(t, fail, D, xbuf, Twc, dx, num_poses, delta_thresh, flags);
   COOP_TICK(5);
+#ifdef M3R_COOP_PROF
   if (t == 0) {
     for (int k = 0; k < 6; k++) g_coop_prof[k] += prof_acc[k];
     for (int k = 0; k < 6; k++) g_coop_prof[8 + k] += aprof[k];
@@ -567,4 +582,5 @@ __global__ void __launch_bounds__(kCoopThreads)
     g_coop_prof[11] += tprof[0], g_coop_prof[12] += tprof[1];
     g_coop_prof[14] += tprof[2], g_coop_prof[15] += tprof[3];
   }
+#endif
 }

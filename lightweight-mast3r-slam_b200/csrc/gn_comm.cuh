@@ -51,9 +51,13 @@ struct CommSlices {
 
 // "my buffer of round `round` is complete": one release store per peer.  The buffer was written
 // by earlier kernels on this stream (visible at the device's L2, which is where peer reads land).
-__global__ void comm_signal_kernel(const CommTable T, int rank, int world, int round,
-                                   const int *__restrict__ stop, int flag_set) {
-  if (stop[0]) return;
+// The handshake (this signal and the wait in the reduce kernels) runs in EVERY round, also after
+// the solve has converged and the data movement is skipped: the wait of round r+1 is what proves
+// that every peer has finished reading this rank's buf[r & 1] before round r+2 overwrites it, and
+// the host-side round counter advances whether or not the device still iterates.  A call that
+// stops early therefore leaves the flags in step with the counter, whatever the parity of the
+// rounds it skipped, and the next call on the same communicator starts from a clean handshake.
+__global__ void comm_signal_kernel(const CommTable T, int rank, int world, int round, int flag_set) {
   const int p = threadIdx.x;
   if (p < world) {
     __threadfence_system();
@@ -83,16 +87,30 @@ __device__ __forceinline__ bool comm_wait_all(const CommTable &T, int rank, int 
 
 __device__ __forceinline__ int comm_row_len(int r, int D) { return (r < D) ? 7 * (r / 7 + 1) : D; }
 
+// A peer did not arrive: report it (flags[3], read by m3r_gn_iterations_done) and stop the solve --
+// with flags[0] set the linearisation, the factorisation and the retraction that are already
+// enqueued behind this kernel return at their first instruction, so Twc is not updated from a
+// stale or partly written system.  m3r_gn_begin clears both.
+__device__ __forceinline__ void comm_fail(int *ws_flags) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    ws_flags[3] = kGnErrExchangeTimeout;
+    ws_flags[2] = 1;
+    __threadfence();
+    ws_flags[0] = 1;
+  }
+}
+
 // two-phase, phase 1: reduce this rank's rows over all ranks' buffers into red[par][rank]
 __global__ void __launch_bounds__(256)
     comm_reduce_scatter_kernel(const CommTable T, const CommSlices S, int rank, int world, int round,
                                int D, int *__restrict__ ws_flags) {
-  if (ws_flags[0]) return;
   __shared__ int timed_out;
+  const bool stopped = ws_flags[0] != 0;  // read before the wait: comm_fail() of another CTA sets it
   if (!comm_wait_all(T, rank, world, round, 0, &timed_out)) {
-    if (threadIdx.x == 0) ws_flags[3] = 1;
+    comm_fail(ws_flags);
     return;
   }
+  if (stopped) return;  // converged earlier: handshake only
   const int par = round & 1;
   double *dst = T.red[par][rank];
   for (int r = S.begin[rank] + blockIdx.x; r < S.begin[rank + 1]; r += gridDim.x) {
@@ -110,12 +128,13 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     comm_gather_kernel(const CommTable T, const CommSlices S, int rank, int world, int round,
                        double *__restrict__ out, int D, int *__restrict__ ws_flags) {
-  if (ws_flags[0]) return;
   __shared__ int timed_out;
+  const bool stopped = ws_flags[0] != 0;
   if (!comm_wait_all(T, rank, world, round, 1, &timed_out)) {
-    if (threadIdx.x == 0) ws_flags[3] = 1;
+    comm_fail(ws_flags);
     return;
   }
+  if (stopped) return;
   const int par = round & 1;
   for (int r = blockIdx.x; r <= D; r += gridDim.x) {
     int p = 0;
@@ -134,12 +153,13 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     comm_reduce_kernel(const CommTable T, int rank, int world, int round, double *__restrict__ out,
                        int D, int *__restrict__ ws_flags) {
-  if (ws_flags[0]) return;
   __shared__ int timed_out;
+  const bool stopped = ws_flags[0] != 0;
   if (!comm_wait_all(T, rank, world, round, 0, &timed_out)) {
-    if (threadIdx.x == 0) ws_flags[3] = 1;
+    comm_fail(ws_flags);
     return;
   }
+  if (stopped) return;
   const int par = round & 1;
   for (int r = blockIdx.x; r <= D; r += gridDim.x) {  // row D = the right-hand side
     const int len = (r < D) ? 7 * (r / 7 + 1) : D;
@@ -279,7 +299,7 @@ extern "C" int m3r_gn_comm_signal(m3r_gn_comm *c, m3r_gn_workspace *ws, void *st
   M3R_REQUIRE(c && ws, "gn_comm_signal: null pointer");
   M3R_REQUIRE(c->connected && c->round > 0, "gn_comm_signal: no round in progress");
   m3r::comm_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->table, c->rank, c->world,
-                                                                         c->round, ws->flags, 0);
+                                                                         c->round, 0);
   M3R_LAUNCH_CHECK("comm_signal_kernel");
   return M3R_OK;
 }
@@ -313,7 +333,7 @@ extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *
     m3r::comm_reduce_scatter_kernel<<<rs_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, D,
                                                              ws->flags);
     M3R_LAUNCH_CHECK("comm_reduce_scatter_kernel");
-    m3r::comm_signal_kernel<<<1, 32, 0, s>>>(c->table, c->rank, c->world, c->round, ws->flags, 1);
+    m3r::comm_signal_kernel<<<1, 32, 0, s>>>(c->table, c->rank, c->world, c->round, 1);
     M3R_LAUNCH_CHECK("comm_signal_kernel");
     const int ag_blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
     m3r::comm_gather_kernel<<<ag_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, out, D,

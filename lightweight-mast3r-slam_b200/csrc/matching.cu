@@ -592,13 +592,14 @@ __device__ __forceinline__ unsigned long long gtime() {
 // order computed by every CTA from the flag array), and reads its box from the plan instead of
 // reducing it, so the TMA copies start at the first instruction instead of after a dependent
 // p1 load and two barriers.
-constexpr int kRtMaxPlanned = 4096;  // tiles the flag scan of the main kernel covers (16 per thread)
+constexpr int kRtMaxPlanned = 16 * kRtThreads;  // tiles the flag scan of the main kernel covers (16 per thread)
 // The order only pays while a launch is a few rounds of 2 x 148 CTAs long.  Measured at 512x384
 // (768 tiles per image), planned against unplanned: b = 1: 135 / 147 us, b = 2: 242 / 242, b = 3:
 // 354 / 369, b = 4: 455 / 474, b = 5: 569 / 553, b = 8 (with a wider scan): 902 / 859: with many
 // rounds the heavy tiles are spread by the index order anyway, and taking them first puts two of
 // them on the same SM.  Above this many tiles the unplanned grid of tiles is launched.
-constexpr int kRtPlanUpTo = 3200;
+constexpr int kRtPlanUpTo = kRtMaxPlanned < 3200 ? kRtMaxPlanned : 3200;
+static_assert(kRtPlanUpTo <= 16 * kRtThreads, "the flag scan covers 16 tiles per thread of the main kernel");
 __global__ void __launch_bounds__(kRtThreads)
     refine_plan_kernel(const long long *__restrict__ p1, int4 *__restrict__ plan,
                        unsigned char *__restrict__ heavy, int h, int w, int dilation_max, int tiles_x,
@@ -992,7 +993,6 @@ static int launch_refine_tiled(const __half *D11, const __half *D21, const long 
   const int tiles_x = (w + kRtQ - 1) / kRtQ, tiles_y = (h + kRtQy - 1) / kRtQy;
   const long long ntiles = static_cast<long long>(b) * tiles_x * tiles_y;
   M3R_REQUIRE(tiles_y <= 65535, "refine_matches: image too tall");
-  static_assert(kRtPlanUpTo <= kRtMaxPlanned, "flag scan too narrow");
   if (planned && ntiles <= kRtPlanUpTo) {
     // stream-ordered scratch: one int4 box per tile, then the flag bytes padded to 16 per thread
     // (from a private pool that keeps its memory across host synchronisations: the default
@@ -1017,7 +1017,8 @@ static int launch_refine_tiled(const __half *D11, const __half *D21, const long 
     }
     const size_t plan_bytes = static_cast<size_t>(ntiles) * sizeof(int4);
     void *scratch = nullptr;
-    M3R_CUDA_TRY(cudaMallocFromPoolAsync(&scratch, plan_bytes + kRtThreads * 16, pool, s));
+    // flag bytes: every thread of the main kernel loads 16 of them as one uint4, whatever ntiles is
+    M3R_CUDA_TRY(cudaMallocFromPoolAsync(&scratch, plan_bytes + kRtMaxPlanned, pool, s));
     int4 *plan = static_cast<int4 *>(scratch);
     unsigned char *heavy = static_cast<unsigned char *>(scratch) + plan_bytes;
     const int nt = static_cast<int>(ntiles);

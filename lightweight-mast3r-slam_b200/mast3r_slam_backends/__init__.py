@@ -148,13 +148,24 @@ _ws_lock = threading.Lock()
 
 
 def _workspace(device):
-    key = (device.index if device.index is not None else torch.cuda.current_device(),
-           threading.get_ident())
+    """One workspace per (device, host thread, CUDA stream): the scratch (partials, per-edge blocks,
+    system, flags, compacted lists) is ordered only by the stream the calls are enqueued on, so two
+    streams must never share it (the reference serialised everything on the legacy default
+    stream).  `release_workspaces()` frees them."""
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (index, threading.get_ident(), torch.cuda.current_stream(index).cuda_stream)
     with _ws_lock:
         ws = _workspaces.get(key)
         if ws is None:
             ws = _workspaces[key] = _Workspace(device)
     return ws
+
+
+def release_workspaces():
+    """Free every cached Gauss-Newton workspace (device scratch grows to the largest graph seen).
+    The caller must have synchronised the streams that used them."""
+    with _ws_lock:
+        _workspaces.clear()
 
 
 def _gn_common_checks(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, extra=None):

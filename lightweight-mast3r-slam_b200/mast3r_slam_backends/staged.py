@@ -218,4 +218,7 @@ def gauss_newton_sharded(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_sh
     gn = StagedGN(kind, Twc, Xs, Cs, ii, jj, idx_shard, valid_shard, Q_shard,
                   edge_begin=begin, edge_end=end, **params)
     run_spmd(gn, exchange if exchange is not None else TorchAllReduce(group), max_iter, delta_thresh)
+    # raises if a peer never arrived (the device then stopped the solve before touching Twc again)
+    # or if ii/jj name more keyframes than Twc holds; synchronises this rank's stream
+    gn.iterations_done()
     return [gn.dx], gn

@@ -139,7 +139,11 @@ def test_alternative_solvers(solver):
             "    e_dx, e_T = t._solver_check(be, m3r_oracle, N)\n"
             "    assert e_dx < t.TOL and e_T < t.TOL, (N, e_dx, e_T)\n"
             "print('ok')\n") % [p for p in sys.path if p]
-    env = dict(os.environ, M3R_GN_SOLVER=solver)
+    variants = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_variants", "libm3r_b200_variants.so")
+    if not os.path.exists(variants):
+        pytest.skip("tests/_variants/libm3r_b200_variants.so not built (lightweight-mast3r-slam_b200/build.py)")
+    # the alternative solvers are not in the product library: they live in the variants build
+    env = dict(os.environ, M3R_GN_SOLVER=solver, M3R_B200_LIB=variants)
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
