@@ -223,8 +223,9 @@ def time_matching(be, sets, M, steps, warmup, world, per_kernel=True):
     t1.record()
     torch.cuda.synchronize()
     barrier(world)
-    total_ms = max_over_ranks(t0.elapsed_time(t1), world)
-    out = {"total_ms": total_ms}
+    mine = t0.elapsed_time(t1)
+    total_ms = max_over_ranks(mine, world)
+    out = {"total_ms": total_ms, "rank_ms": mine}
     if per_kernel:
         out["iter_proj_ms"] = statistics.mean(e[0].elapsed_time(e[1]) for e in ev)
         out["cast_ms"] = statistics.mean(e[1].elapsed_time(e[2]) for e in ev)
@@ -497,12 +498,26 @@ def gn_kwargs(g, D):
                 sigma_point=D["sigma_point"], C_thresh=D["C_thresh"], Q_thresh=D["Q_thresh"])
 
 
+GN_CALLS = {
+    "rays": lambda be, g, D, T, iters: be.gauss_newton_rays(
+        T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], D["sigma_ray"],
+        D["sigma_dist"], D["C_thresh"], D["Q_thresh"], iters, 0.0),
+    "calib": lambda be, g, D, T, iters: be.gauss_newton_calib(
+        T, g["Xs"], g["Cs"], g["K"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], g["h"], g["w"],
+        D["pixel_border"], D["z_eps"], D["sigma_pixel"], D["sigma_depth"], D["C_thresh"], D["Q_thresh"], iters, 0.0),
+    "points": lambda be, g, D, T, iters: be.gauss_newton_points(
+        T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], D["sigma_point"],
+        D["C_thresh"], D["Q_thresh"], iters, 0.0),
+}
+
+
 def time_gn(g, D, kind, rank, world, iters=10, reps=3, exchange="peer"):
     """One gauss_newton_<kind> solve of `iters` iterations (delta_thresh = 0), through the
     staged C ABI so that the accumulation/assembly half and the solve half of every iteration
     get their own CUDA events.  At world > 1 each rank linearises its edge shard and the fp64
     systems are summed over the ranks before the replicated solve: `exchange` = "peer" (this
-    library's NVLink peer-memory kernels) or "nccl" (torch.distributed all_reduce)."""
+    library's NVLink peer-memory kernels) or "nccl" (torch.distributed all_reduce).
+    Returns the repetition with the smallest total (of `reps`, after one warm-up)."""
     from mast3r_slam_backends.staged import PeerExchange, StagedGN, TorchAllReduce, shard_range
 
     E = g["E"]
@@ -545,34 +560,104 @@ def time_gn(g, D, kind, rank, world, iters=10, reps=3, exchange="peer"):
                  iters_done=gn.iterations_done(), Twc=Twc)
         if best is None or r["total_ms"] < best["total_ms"]:
             best = r
+    del ex
     return best
 
 
-def time_gn_single_call(be, g, D, kind, iters=10):
-    """The drop-in export itself (one host call, no events inside)."""
+def time_gn_single_call(be, g, D, kind, iters=10, reps=3):
+    """The drop-in export itself (one host call, no events inside); smallest of `reps`."""
     Twc = g["Twc_init"].clone()
-    fn = dict(rays=lambda T: be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
-                                                  g["valid_match"], g["Q"], D["sigma_ray"], D["sigma_dist"],
-                                                  D["C_thresh"], D["Q_thresh"], iters, 0.0),
-              calib=lambda T: be.gauss_newton_calib(T, g["Xs"], g["Cs"], g["K"], g["ii"], g["jj"],
-                                                    g["idx_ii2jj"], g["valid_match"], g["Q"], g["h"], g["w"],
-                                                    D["pixel_border"], D["z_eps"], D["sigma_pixel"],
-                                                    D["sigma_depth"], D["C_thresh"], D["Q_thresh"], iters, 0.0),
-              points=lambda T: be.gauss_newton_points(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
-                                                      g["valid_match"], g["Q"], D["sigma_point"],
-                                                      D["C_thresh"], D["Q_thresh"], iters, 0.0))[kind]
-    fn(Twc)  # warm-up (allocations)
+    GN_CALLS[kind](be, g, D, Twc, iters)  # warm-up (allocations)
     best = 1e30
-    for _ in range(3):
+    for _ in range(reps):
         Twc = g["Twc_init"].clone()
         torch.cuda.synchronize()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
-        fn(Twc)
+        GN_CALLS[kind](be, g, D, Twc, iters)
         t1.record()
         torch.cuda.synchronize()
         best = min(best, t0.elapsed_time(t1))
     return best, Twc
+
+
+def pose_groups(a, b):
+    """Relative difference of Sim(3) states per component group (t against the largest
+    translation, q against 1, s against each pose's scale): the 1e-4 criterion of north_star."""
+    a, b = a.double(), b.double()
+    return {"t": ((a[:, :3] - b[:, :3]).abs().max() / b[:, :3].abs().max().clamp_min(1e-12)).item(),
+            "q": (a[:, 3:7] - b[:, 3:7]).abs().max().item(),
+            "s": ((a[:, 7] - b[:, 7]).abs() / b[:, 7].abs()).max().item()}
+
+
+def gn_parity(be, g, D, kind, Twc_sharded, rank, world, refmod):
+    """Correctness fields of a GN line, at every N: the sharded result against the unsharded
+    solve of the same library (N > 1), bitwise equality of the replicas (N > 1), the
+    reference's own CUDA kernels on the same graph (N = 1, when oracle/_ref is present) and the
+    distance to the poses the scene was generated from."""
+    out = {"pose_err_vs_truth": (Twc_sharded - g["Twc_true"]).abs().max().item(), "tolerance": 1e-4}
+    Twc_1 = None
+    if rank == 0:  # rank 0 holds the whole graph
+        Twc_1 = g["Twc_init"].clone()
+        GN_CALLS[kind](be, g, D, Twc_1, 10)
+        torch.cuda.synchronize()
+    if world > 1:
+        gathered = [torch.empty_like(Twc_sharded) for _ in range(world)]
+        torch.distributed.all_gather(gathered, Twc_sharded.contiguous())
+        if rank == 0:
+            out["replicas_bitwise_equal"] = all(torch.equal(gathered[0], t) for t in gathered[1:])
+            out["max_abs_diff_vs_1gpu"] = (Twc_sharded - Twc_1).abs().max().item()
+            out["rel_diff_vs_1gpu"] = pose_groups(Twc_sharded, Twc_1)
+    if rank == 0 and refmod is not None:
+        Tr = g["Twc_init"].clone()
+        t0 = time.perf_counter()
+        GN_CALLS[kind](refmod, g, D, Tr, 10)
+        torch.cuda.synchronize()
+        out["reference_cuda_ms_per_iter"] = (time.perf_counter() - t0) * 100.0
+        out["max_abs_diff_vs_reference_cuda"] = (Twc_1 - Tr).abs().max().item()
+        out["rel_diff_vs_reference_cuda"] = pose_groups(Twc_1, Tr)
+        out["within_tolerance"] = max(out["rel_diff_vs_reference_cuda"].values()) < 1e-4
+    return out
+
+
+def gn_report(be, g, D, kind, rank, world, peak, refmod, reps=3, nccl_too=True, single_call=True):
+    """One GN configuration: phase times (smallest-total repetition of `reps`), roofline of the
+    linearisation, parity fields, and at N > 1 the NCCL variant beside the peer-memory one."""
+    from mast3r_slam_backends import _lib
+
+    l0 = _lib.launch_count()
+    gr = time_gn(g, D, kind, rank, world, reps=reps)
+    launches = (_lib.launch_count() - l0) // (reps + 1)
+    E, n, N = g["E"], g["n"], g["N"]
+    gn_bytes = B_GN * E * n + 840 * E + 32 * N
+    lin_gbs = gn_bytes / world / (gr["linearize_ms"] * 1e-3) / 1e9
+    out = {
+        "metric": f"GN iters/s (gauss_newton_{kind}, {N}-keyframe graph, {E} directed edges, {g['w']}x{g['h']})",
+        "value": 10 / (gr["total_ms"] * 1e-3), "unit": "iters/s", "scaling": "strong",
+        "stat": f"smallest total of {reps} repetitions of one 10-iteration call (after 1 warm-up call); "
+                "phase times are means over its 10 iterations",
+        "ms_per_iter": gr["total_ms"] / 10, "begin_ms": gr["begin_ms"], "linearize_ms": gr["linearize_ms"],
+        "allreduce_ms": gr["allreduce_ms"], "solve_ms": gr["solve_ms"], "iters_done": gr["iters_done"],
+        "gpu_launches": int(launches), "system_unknowns": 7 * (N - 1),
+        "edges_per_rank": E // world,
+        "exchange": "none" if world == 1 else "NVLink peer memory (m3r_gn_comm_*), fp64 system",
+        "roofline": {"bound": "hbm", "kernel": f"gn_accumulate_kernel<{kind}> (+ edge finalize + assemble)",
+                     "achieved": lin_gbs, "peak": peak, "unit": "GB/s", "frac": lin_gbs / peak,
+                     "traffic": traffic("gn_accumulate_kernel") if (kind == "rays" and N == 64 and world == 1) else None,
+                     "bytes_per_iter": gn_bytes,
+                     "note": "algorithmic = 45 B x E x n per iteration (SURVEY 8d) / ranks; the kernel reads "
+                             "compacted lists and hits L2 on the pointmaps, so DRAM traffic is below it",
+                     "whole_iter_frac": gn_bytes / world / (gr["total_ms"] / 10 * 1e-3) / 1e9 / peak},
+    }
+    out["parity"] = gn_parity(be, g, D, kind, gr["Twc"], rank, world, refmod)
+    if world > 1 and nccl_too:
+        gn2 = time_gn(g, D, kind, rank, world, reps=2, exchange="nccl")
+        out["nccl_variant"] = {"ms_per_iter": gn2["total_ms"] / 10, "allreduce_ms": gn2["allreduce_ms"],
+                               "max_abs_diff_vs_peer": (gn2["Twc"] - gr["Twc"]).abs().max().item()}
+    if world == 1 and single_call:
+        ms_call, _ = time_gn_single_call(be, g, D, kind)
+        out["single_call_ms_per_iter"] = ms_call / 10
+    return out
 
 
 # --------------------------------------------------------------------------------------------
@@ -621,26 +706,41 @@ def cpu_baseline_gn(D, num_kf=8, iters=1):
     return dt / iters, g["E"]
 
 
-def reference_cuda_leg(sets, M, g, D, steps):
+def reference_cuda_leg(ref, sets, M, steps):
     """The UNMODIFIED reference extension (oracle/_ref, sm_100 build of the reference's .cu
-    files) on the same device and inputs: the number the new kernels have to beat."""
-    import refcuda
-
-    ref = refcuda.load_ref()
-    if ref is None:
-        return None
+    files) on the same device and inputs: the number the new kernels have to beat.  (Its GN
+    figure comes from gn_parity, which runs it on the same graph.)"""
     out = {}
     try:
         r = time_matching(ref, sets, M, steps, 3, 1)
         out["matched_px_per_s"] = N_PTS * steps / (r["total_ms"] * 1e-3)
         out["iter_proj_ms"], out["refine_ms"] = r["iter_proj_ms"], r["refine_ms"]
-        if g is not None:
-            ms, _ = time_gn_single_call(ref, g, D, "rays")
-            out["gn_iters_per_s"] = 10 / (ms * 1e-3)
-            out["gn_ms_per_iter"] = ms / 10
     except Exception as exc:  # pragma: no cover
         out["error"] = str(exc)[:200]
     return out
+
+
+def cpu_baseline_tracking_224():
+    """BASELINE configs[0]: the reference's torch tracking GN (tracker.py:173-214, restated in
+    oracle.track_pose_rays and pinned by tests/golden/track_*.npz, which the reference's own
+    tracker.py produced) on a synthetic 224x224 pair with a known Sim(3), on the host cores."""
+    import m3r_oracle as oracle
+    import synth
+
+    t = synth.make_track_inputs(224, 224, seed=0, device="cpu", pose_noise=0.03)
+    torch.set_num_threads(len(os.sched_getaffinity(0)))
+    oracle.track_pose_rays(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"], t["valid_opt"])
+    t0 = time.perf_counter()
+    Tw, _, it, _ = oracle.track_pose_rays(t["Xf"], t["Xk"], t["T_WCf_init"], t["T_WCk"], t["Qk"], t["valid_opt"])
+    dt = time.perf_counter() - t0
+    return {"ms_per_call": dt * 1e3, "iterations": it, "ms_per_iter": dt * 1e3 / max(it, 1),
+            "threads": torch.get_num_threads(),
+            "pose_err_vs_truth": (Tw - t["T_WCf_true"]).abs().max().item(),
+            "pose_err_initial": (t["T_WCf_init"] - t["T_WCf_true"]).abs().max().item()}
+
+
+WORKLOAD = "configs[1]: 512x384 frame-to-keyframe iter_proj + refine_matches, b=1"
+METRIC = "matched px/s (iter_proj + refine_matches, 512x384, b=1)"
 
 
 def run_reference_arm(args, rank, world):
@@ -652,18 +752,74 @@ def run_reference_arm(args, rank, world):
     M = synth.MATCH_DEFAULTS
     pxs, s_per_step, cores = cpu_baseline_matching(M, steps=args.steps, warmup=min(args.warmup, 1))
     line = {
-        "impl": "reference", "metric": "matched px/s (iter_proj + refine_matches, 512x384, b=1)",
+        "impl": "reference", "metric": METRIC,
         "value": pxs, "unit": "px/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": s_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic",
-        "config": {"workload": "configs[1]: 512x384 frame-to-keyframe iter_proj + refine_matches, b=1",
-                   "sample": "whole 512x384 frames"},
+        "config": {"workload": WORKLOAD, "sample": "whole 512x384 frames"},
         "cpu_baseline": {"value": pxs, "unit": "px/s", "cores": cores, "kind": "port",
                          "sample": f"{args.steps} whole 512x384 frame(s); the reference has no CPU "
                                    "implementation (setup.py:47-48), this is oracle/m3r_oracle.c"},
         "e2e": {"value": pxs, "unit": "px/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def host_us_per_call(be, s, M, g16, D, calls=40):
+    """Host cost of one call through the Python shim + ctypes + launch, per export: wall clock over
+    `calls` asynchronous calls issued into an empty stream (the queue never fills), GPU time excluded."""
+    out = {}
+    p, _ = be.iter_proj(s["rays"], s["pts"], s["p_init"], M["max_iter"], M["lambda_init"], M["convergence_thresh"])
+    p1 = p.long()
+
+    def timeit(fn):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(calls):
+            fn()
+        dt = time.perf_counter() - t0
+        torch.cuda.synchronize()
+        return dt / calls * 1e6
+
+    out["iter_proj"] = timeit(lambda: be.iter_proj(s["rays"], s["pts"], s["p_init"], M["max_iter"], M["lambda_init"],
+                                                   M["convergence_thresh"]))
+    out["refine_matches"] = timeit(lambda: be.refine_matches(s["D11"], s["D21"], p1, M["radius"], M["dilation_max"]))
+    if g16 is not None:
+        for kind in ("rays", "calib", "points"):
+            T = g16["Twc_init"].clone()
+            calls_gn = 5
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(calls_gn):
+                GN_CALLS[kind](be, g16, D, T, 10)
+            out[f"gauss_newton_{kind}"] = (time.perf_counter() - t0) / calls_gn * 1e6
+            torch.cuda.synchronize()
+        out["gauss_newton_note"] = "one 10-iteration call on the 16-keyframe graph: 3 + 10 x 5 launches enqueued"
+    return out
+
+
+def host_topology():
+    try:
+        nodes = open("/sys/devices/system/node/online").read().strip()
+    except Exception:
+        nodes = "?"
+    try:
+        topo = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+        rows = [ln for ln in topo.splitlines() if ln.startswith("GPU")]
+        aff = sorted({ln.split("\t")[-3].strip() + "/numa " + ln.split("\t")[-2].strip() for ln in rows if "\t" in ln})
+    except Exception:
+        aff = []
+    return {"numa_nodes_online": nodes, "host_cores_visible": len(os.sched_getaffinity(0)),
+            "gpu_cpu_affinity": aff[:8]}
+
+
+def gather_list(x, world):
+    if world == 1:
+        return [x]
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    out = [torch.empty_like(t) for _ in range(world)]
+    torch.distributed.all_gather(out, t)
+    return [o.item() for o in out]
 
 
 def main():
@@ -675,8 +831,11 @@ def main():
     ap.add_argument("--gn-keyframes", type=int, default=64)
     ap.add_argument("--gn-kind", default="rays", choices=["rays", "calib", "points"])
     ap.add_argument("--skip-gn", action="store_true")
+    ap.add_argument("--skip-gn-configs", action="store_true",
+                    help="only the headline 64-keyframe graph, not BASELINE configs[2..4]")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-refcuda", action="store_true")
+    ap.add_argument("--skip-extras", action="store_true", help="no front-end / tracking / frame-pipeline legs")
     ap.add_argument("--profile", action="store_true",
                     help="wrap the timed regions in cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     ap.add_argument("--iter-proj-variant", type=int, default=0)
@@ -705,21 +864,32 @@ def main():
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     M, D = synth.MATCH_DEFAULTS, synth.GN_DEFAULTS
     peak, peak_src = peaks()
+    refmod = None
+    if rank == 0 and world == 1 and not args.skip_refcuda:
+        import refcuda
+
+        refmod = refcuda.load_ref()
 
     # ---- matching: K steps, inputs rotated over NUM_SETS frame sets (cold in L2)
     sets = make_match_sets("cuda", NUM_SETS, seed0=100 * rank)
-    sampler = ClockSampler(local_rank)
-    time_matching(be, sets, M, 20, 5, world)  # clocks up
-    sampler.start()
+    sampler = ClockSampler(local_rank) if rank == 0 else None  # one sampler per job, not per rank
+    time_matching(be, sets, M, 20, 5, world, per_kernel=False)  # clocks up
+    if sampler:
+        sampler.start()
     l0 = _lib.launch_count()
     if args.profile:
         torch.cuda.synchronize()
         torch.cuda.profiler.start()
-    r = time_matching(be, sets, M, args.steps, args.warmup, world)
+    # the headline loop carries no per-kernel events: K x (iter_proj, cast, refine_matches)
+    # between one pair of events.  The per-kernel durations come from a second pass.
+    r = time_matching(be, sets, M, args.steps, args.warmup, world, per_kernel=False)
     if args.profile:
         torch.cuda.profiler.stop()
     launches = (_lib.launch_count() - l0) * args.steps // (args.steps + args.warmup)  # same launches every step
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler else None
+    rank_ms = gather_list(r["rank_ms"] / args.steps, world)
+    rk = time_matching(be, sets, M, min(args.steps, 100), 3, world, per_kernel=True)
+    r.update({k: v for k, v in rk.items() if k.endswith("_ms") and k not in ("total_ms", "rank_ms")})
     ms_step = r["total_ms"] / args.steps
     value = world * N_PTS / (ms_step * 1e-3)
     e2e_steps = max(args.steps, 60)  # long enough that pipeline fill and drain are noise
@@ -732,22 +902,24 @@ def main():
     half_macs = N_PTS * 245 * FDIM  # radius 3, dilation 5: 245 windows x 24 MACs per point
 
     line = {
-        "metric": "matched px/s (iter_proj + refine_matches, 512x384, b=1)", "value": value,
+        "metric": METRIC, "value": value,
         "unit": "px/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32 (iter_proj) + f16 per-op rounded (refine_matches) + f32/f64 (GN)",
         "data": "synthetic",
-        "config": {"workload": "configs[1]: 512x384 frame-to-keyframe iter_proj + refine_matches, b=1; "
-                               "matching runs as independent replicas per GPU",
+        "config": {"workload": WORKLOAD,
+                   "replicas": "matching runs as independent replicas per GPU (b = 1 does not shard, SURVEY 8e)",
                    "l2": f"inputs rotated over {NUM_SETS} frame sets ({NUM_SETS}x38 MB > 126 MB L2)",
                    "params": M},
         "clocks": clocks,
+        "per_rank_ms_per_step": {"min": min(rank_ms), "median": statistics.median(rank_ms), "max": max(rank_ms)},
         "e2e": {"value": e2e_value, "unit": "px/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / e2e_steps,
                 "mode": "streamed: H2D of frame i+1 and D2H of frame i-1 overlap the kernels of frame i "
                         "(double-buffered, three streams); all copies inside the timed region",
                 "serial_ms_per_step": e2e_serial_ms / e2e_steps,
-                "serial_value": world * N_PTS * e2e_steps / (e2e_serial_ms * 1e-3)},
+                "serial_value": world * N_PTS * e2e_steps / (e2e_serial_ms * 1e-3),
+                "host": host_topology() if rank == 0 else None},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "refine_f16_tiled_kernel", "achieved": refine_gbs,
                      "peak": peak, "unit": "GB/s", "frac": refine_gbs / peak,
@@ -761,74 +933,76 @@ def main():
                      "fp16_pipe_frac": (2 * half_macs / 2 / 32) / (148 * 4 * 0.486 * 1.965e9) /
                                        (r["refine_ms"] * 1e-3),
                      # 245 windows x 3 LDS.128 per point, 4 wavefronts per warp-wide LDS.128 when
-                     # conflict-free, one wavefront per clock per SM; the ncu capture shows 1.44x
-                     # this many wavefronts (bank-conflict replays of a noisy gather)
+                     # conflict-free, one wavefront per clock per SM
                      "smem_pipe_frac_conflict_free": (N_PTS / 32 * 245 * 3 * 4) / (148 * 1.965e9) /
                                                      (r["refine_ms"] * 1e-3)},
         "kernels": {"iter_proj_ms": r["iter_proj_ms"], "cast_ms": r["cast_ms"], "refine_ms": r["refine_ms"],
                     "iter_proj_gbs": iproj_gbs, "iter_proj_frac": iproj_gbs / peak,
-                    "pair_gbs": pair_gbs, "pair_frac": pair_gbs / peak},
+                    "pair_gbs": pair_gbs, "pair_frac": pair_gbs / peak,
+                    "note": "per-kernel durations from a second pass with events around each call; the "
+                            "headline loop has one pair of events around all K steps"},
     }
 
-    if rank == 0 and not args.profile:
+    extras = not (args.profile or args.skip_extras)
+    if rank == 0 and extras:
         line["front_end"] = time_front_end(be, sets, M, max(args.steps // 4, 10), 3)
-    if not args.profile:
+    if extras:
         fe = time_front_e2e(sets, M, e2e_steps, 3, world)
         if rank == 0:
             line["front_end"]["e2e"] = fe
-    if rank == 0 and not args.profile:
+    if rank == 0 and extras:
         line["tracking"] = time_tracking(max(args.steps // 4, 10), 3)
         line["frame_pipeline"] = time_frame_pipeline(sets, M, max(args.steps // 2, 20), 3)
 
-    # ---- Gauss-Newton
+    # ---- Gauss-Newton: the headline graph (64 keyframes, rays) and BASELINE configs[2..4]
     g = None
     if not args.skip_gn:
         g = make_gn_graph(args.gn_keyframes, "cuda", seed=0)
-        l0 = _lib.launch_count()
         if args.profile:
             torch.cuda.synchronize()
             torch.cuda.profiler.start()
-        gr = time_gn(g, D, args.gn_kind, rank, world, reps=1 if args.profile else 3)
+        line["gn"] = gn_report(be, g, D, args.gn_kind, rank, world, peak, refmod, reps=1 if args.profile else 3)
         if args.profile:
             torch.cuda.profiler.stop()
-        gn_launches = (_lib.launch_count() - l0) // (2 if args.profile else 4)
-        E, n, N = g["E"], g["n"], g["N"]
-        gn_bytes = B_GN * E * n + 840 * E + 32 * N
-        lin_gbs = gn_bytes / world / (gr["linearize_ms"] * 1e-3) / 1e9
-        line["gn"] = {
-            "metric": f"GN iters/s (gauss_newton_{args.gn_kind}, {N}-keyframe graph, {E} directed edges, 512x384)",
-            "value": 10 / (gr["total_ms"] * 1e-3), "unit": "iters/s", "scaling": "strong",
-            "ms_per_iter": gr["total_ms"] / 10, "linearize_ms": gr["linearize_ms"],
-            "allreduce_ms": gr["allreduce_ms"], "solve_ms": gr["solve_ms"],
-            "iters_done": gr["iters_done"], "gpu_launches": int(gn_launches),
-            "roofline": {"bound": "hbm", "kernel": "gn_accumulate_kernel (+edge finalize + assemble)",
-                         "achieved": lin_gbs, "peak": peak, "unit": "GB/s", "frac": lin_gbs / peak,
-                         "traffic": traffic("gn_accumulate_kernel"), "bytes_per_iter": gn_bytes,
-                         "note": "algorithmic = 45 B x E x n (SURVEY 8d); the kernel reads compacted "
-                                 "lists and hits L2 on the pointmaps, so DRAM traffic is below it",
-                         "whole_iter_frac": gn_bytes / world / (gr["total_ms"] / 10 * 1e-3) / 1e9 / peak},
-        }
-        line["gn"]["begin_ms"] = gr["begin_ms"]
-        line["gn"]["exchange"] = "none" if world == 1 else "NVLink peer memory (m3r_gn_comm_*), fp64 system"
-        if world > 1:  # the same sharded solve with torch.distributed's NCCL all-reduce, beside it
-            gn2 = time_gn(g, D, args.gn_kind, rank, world, reps=2, exchange="nccl")
-            line["gn"]["nccl_variant"] = {"ms_per_iter": gn2["total_ms"] / 10,
-                                          "allreduce_ms": gn2["allreduce_ms"]}
-        if world == 1:
-            ms_call, Tcall = time_gn_single_call(be, g, D, args.gn_kind)
-            line["gn"]["single_call_ms_per_iter"] = ms_call / 10
-            line["gn"]["pose_err_vs_truth"] = (Tcall - g["Twc_true"]).abs().max().item()
+        if not (args.profile or args.skip_gn_configs):
+            cfgs = {}
+            # configs[3]: the same 64-keyframe graph through the calibrated solver, sharded at N > 1
+            cfgs["calib64"] = gn_report(be, g, D, "calib", rank, world, peak, refmod, single_call=False)
+            if rank == 0 and world == 1 and refmod is not None:
+                line["reference_cuda"] = reference_cuda_leg(refmod, sets, M, min(args.steps, 50))
+                line["reference_cuda"]["gn_ms_per_iter"] = line["gn"]["parity"].get("reference_cuda_ms_per_iter")
+                if line["reference_cuda"]["gn_ms_per_iter"]:
+                    line["reference_cuda"]["gn_iters_per_s"] = 1e3 / line["reference_cuda"]["gn_ms_per_iter"]
+            del g
+            torch.cuda.empty_cache()
+            # configs[2]: 16-keyframe rays graph
+            g16 = make_gn_graph(16, "cuda", seed=0)
+            cfgs["rays16"] = gn_report(be, g16, D, "rays", rank, world, peak, refmod, single_call=False)
+            if rank == 0:
+                line["host_us_per_call"] = host_us_per_call(be, sets[0], M, g16, D)
+            del g16
+            torch.cuda.empty_cache()
+            # configs[4]: 256-keyframe loop-closure graph, gauss_newton_points, D = 1785
+            g256 = make_gn_graph(256, "cuda", seed=0)
+            cfgs["points256"] = gn_report(be, g256, D, "points", rank, world, peak, refmod, reps=2,
+                                          single_call=False)
+            del g256
+            torch.cuda.empty_cache()
+            line["gn_configs"] = cfgs
+            g = None
+    elif rank == 0 and world == 1 and refmod is not None:
+        line["reference_cuda"] = reference_cuda_leg(refmod, sets, M, min(args.steps, 50))
 
-    if rank == 0 and world == 1 and not args.skip_refcuda:
-        line["reference_cuda"] = reference_cuda_leg(sets, M, g, D, min(args.steps, 50))
     if rank == 0 and world == 1 and not args.skip_cpu:
         pxs, s_per, cores = cpu_baseline_matching(M, steps=2, warmup=1)
         line["cpu_baseline"] = {"value": pxs, "unit": "px/s", "cores": cores, "kind": "port",
                                 "sample": "2 whole 512x384 frames (oracle/m3r_oracle.c, OpenMP)"}
         if not args.skip_gn:
             s_it, Ecpu = cpu_baseline_gn(D)
-            line["cpu_baseline"]["gn_iters_per_s_64kf_extrapolated"] = 1.0 / (s_it * g["E"] / Ecpu)
+            E64 = line["gn"]["roofline"]["bytes_per_iter"] // (B_GN * N_PTS)
+            line["cpu_baseline"]["gn_iters_per_s_64kf_extrapolated"] = 1.0 / (s_it * E64 / Ecpu)
             line["cpu_baseline"]["gn_sample"] = f"1 iteration, 8-keyframe graph ({Ecpu} edges), scaled by edges"
+            line["cpu_baseline"]["tracking_224x224"] = cpu_baseline_tracking_224()
     if saved_stdout is not None:
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
