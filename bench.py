@@ -595,7 +595,8 @@ def gn_parity(be, g, D, kind, Twc_sharded, rank, world, refmod):
     solve of the same library (N > 1), bitwise equality of the replicas (N > 1), the
     reference's own CUDA kernels on the same graph (N = 1, when oracle/_ref is present) and the
     distance to the poses the scene was generated from."""
-    out = {"pose_err_vs_truth": (Twc_sharded - g["Twc_true"]).abs().max().item(), "tolerance": 1e-4}
+    out = {"pose_err_vs_truth": (Twc_sharded - g["Twc_true"]).abs().max().item(),
+           "tolerance_vs_reference": 1e-4}
     Twc_1 = None
     if rank == 0:  # rank 0 holds the whole graph
         Twc_1 = g["Twc_init"].clone()
