@@ -378,6 +378,38 @@ int m3r_gn_comm_reduce(m3r_gn_comm *comm, m3r_gn_workspace *ws, double *out, int
  * Process-wide; for tests and benchmarks. */
 void m3r_debug_set_exchange_mode(int mode);
 
+/* ---------------------------------------------------------------------------------------
+ * Single-process multi-GPU Gauss-Newton (new).  The reference's caller
+ * (global_opt.py:142-143, one backend process, main.py:268) hands over tensors on ONE device;
+ * this handle lets that unchanged call use several devices of the box.
+ *
+ *   devices[0] is the device the caller's tensors live on.  The other devices read those
+ *   tensors in place over NVLink peer access during their per-call preparation (packing Xs / Cs
+ *   and compacting their shard's rows of idx_ii2jj / valid_match / Q into local memory: that
+ *   pass is the scatter, nothing is staged), then run every iteration from local memory:
+ *   linearise the shard -> m3r_gn_comm exchange (rank order, bitwise identical sums) ->
+ *   replicated solve and retraction.  Rank 0 updates the caller's Twc in place.
+ *   A device may be listed more than once (loop-back ranks on one GPU, each with its own
+ *   workspace, exchange area and stream): the 1-GPU tests run the protocol that way.
+ *
+ * m3r_gn_multi_solve: `prob` as for m3r_gn_begin with every pointer on devices[0] and the WHOLE
+ * edge arrays (edge_begin / edge_end are ignored); `stream` is a stream of devices[0].  The other
+ * devices' streams are ordered after the work already enqueued on `stream`, and `stream` is
+ * ordered after their completion, so the caller keeps ordinary stream semantics.  Never blocks
+ * the host (except when the graph outgrows the exchange areas, which are then re-allocated).
+ * ------------------------------------------------------------------------------------- */
+typedef struct m3r_gn_multi m3r_gn_multi;
+int m3r_gn_multi_create(m3r_gn_multi **out, const int *devices, int num_devices);
+void m3r_gn_multi_destroy(m3r_gn_multi *multi);
+int m3r_gn_multi_solve(m3r_gn_multi *multi, const m3r_gn_problem *prob, float *dx, int max_iter,
+                       float delta_thresh, void *stream);
+/* After a solve (synchronises every rank; tests and benchmarks): iterations executed, the time
+ * each rank's preparation took in ms (begin_ms[num_devices]; for ranks > 0 this is the scatter:
+ * remote reads + packing + compaction), and whether every rank's pose replica equals `Twc`
+ * (device pointer on devices[0]) bit for bit.  Any of the outputs may be null. */
+int m3r_gn_multi_report(m3r_gn_multi *multi, const float *Twc, int num_poses, float *begin_ms,
+                        int *iters, int *replicas_equal);
+
 #ifdef __cplusplus
 }
 #endif

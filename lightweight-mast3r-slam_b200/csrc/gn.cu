@@ -27,6 +27,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "sim3.cuh"
 
@@ -256,11 +257,14 @@ constexpr int kChunk = kSeg * kAccWarps;    // points per work item (one CTA pas
 
 __global__ void __launch_bounds__(256)
     gn_pack_kernel(const float *__restrict__ Xs, const float *__restrict__ Cs,
-                   float4 *__restrict__ P, size_t total) {
+                   float4 *__restrict__ P, float *__restrict__ cs_copy, size_t total) {
+  // cs_copy: local copy of Cs for the compaction's gathers when Xs / Cs live on another device
+  // (single-process multi-GPU, gn_multi.cuh); null otherwise
   for (size_t k = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < total;
        k += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    P[k] = make_float4(__ldcs(Xs + 3 * k), __ldcs(Xs + 3 * k + 1), __ldcs(Xs + 3 * k + 2),
-                       __ldcs(Cs + k));
+    const float c = __ldcs(Cs + k);
+    P[k] = make_float4(__ldcs(Xs + 3 * k), __ldcs(Xs + 3 * k + 1), __ldcs(Xs + 3 * k + 2), c);
+    if (cs_copy) cs_copy[k] = c;
   }
 }
 
@@ -1160,6 +1164,8 @@ struct m3r_gn_workspace {
   DevBuf<int> pose_i, pose_j;     // [E] packed pose index per directed edge
   DevBuf<unsigned char> first;    // [2E] scratch of the id remap
   DevBuf<float4> packed;          // [N, n] (x, y, z, c) records of every keyframe point
+  DevBuf<float> cs_copy;          // [N, n] local copy of Cs (copy_cs: the caller's Cs is on a peer device)
+  bool copy_cs = false;
   DevBuf<int> ck, cidx;           // [items * kChunk] compacted match lists (point k, match idx)
   DevBuf<float> cq;               //                  and their confidences
   DevBuf<int> counts;             // [items * kAccWarps] entries per warp segment
@@ -1175,6 +1181,7 @@ struct m3r_gn_workspace {
 };
 
 #include "gn_comm.cuh"
+#include "gn_multi.cuh"
 
 extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
   M3R_REQUIRE(out != nullptr, "gn_workspace_create: null out pointer");
@@ -1193,6 +1200,7 @@ extern "C" int m3r_gn_workspace_create(m3r_gn_workspace **out) {
 extern "C" void m3r_gn_workspace_destroy(m3r_gn_workspace *ws) {
   if (!ws) return;
   ws->pose_i.release(), ws->pose_j.release(), ws->first.release(), ws->partials.release();
+  ws->cs_copy.release();
   ws->packed.release(), ws->ck.release(), ws->cidx.release(), ws->cq.release(), ws->counts.release();
   ws->edge_H.release(), ws->edge_g.release(), ws->system.release(), ws->ldiag.release();
   ws->xbuf.release();
@@ -1260,20 +1268,35 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
   M3R_REQUIRE(items * kAccWarps < (1ull << 31), "gn_begin: shard too large (%zu items)", items);
   const size_t total = static_cast<size_t>(prob->num_poses) * n;
   if ((rc = ws->packed.reserve(total))) return rc;
+  if (ws->copy_cs && (rc = ws->cs_copy.reserve(total))) return rc;
   if ((rc = ws->ck.reserve(items * kChunk + 1))) return rc;
   if ((rc = ws->cidx.reserve(items * kChunk + 1))) return rc;
   if ((rc = ws->cq.reserve(items * kChunk + 1))) return rc;
   if ((rc = ws->counts.reserve(items * kAccWarps + 1))) return rc;
+  // Everything m3r_gn_linearize and m3r_gn_solve_retract use is reserved HERE, before any kernel of
+  // the call is enqueued: growing a buffer means cudaFree + cudaMalloc, which synchronise the
+  // device, and once the multi-GPU exchange is running a kernel may be spinning on a peer's flag
+  // whose signal this host thread has not enqueued yet (ranks that share a process: the single-
+  // process multi-GPU driver and the loop-back tests) -- the host would block on the device, the
+  // device on the host, until the exchange times out.  After m3r_gn_begin the stages never allocate.
+  {
+    const int D = 7 * (prob->num_poses - 1);
+    if ((rc = ws->partials.reserve(items * kNAcc + 1))) return rc;
+    if ((rc = ws->edge_H.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 49))) return rc;
+    if ((rc = ws->edge_g.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 7))) return rc;
+    if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
+    if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride))) return rc;
+  }
   {
     const size_t want_blocks = (total + 255) / 256;
     const size_t cap = static_cast<size_t>(kNumSMs) * 16;
     gn_pack_kernel<<<static_cast<int>(want_blocks < cap ? want_blocks : cap), 256, 0, s>>>(
-        prob->Xs, prob->Cs, ws->packed.p, total);
+        prob->Xs, prob->Cs, ws->packed.p, ws->copy_cs ? ws->cs_copy.p : nullptr, total);
     M3R_LAUNCH_CHECK("gn_pack_kernel");
   }
   if (items > 0) {
     CompactArgs c{};
-    c.Cs = prob->Cs;
+    c.Cs = ws->copy_cs ? ws->cs_copy.p : prob->Cs;
     c.idx = reinterpret_cast<const long long *>(prob->idx_ii2jj);
     c.valid = prob->valid_match;
     c.Q = prob->Q;

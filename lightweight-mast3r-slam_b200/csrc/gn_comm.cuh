@@ -65,6 +65,15 @@ __global__ void comm_signal_kernel(const CommTable T, int rank, int world, int r
   }
 }
 
+// wall clock in ns, the same on every SM (clock64() is a per-SM cycle counter: it is neither
+// comparable between SMs nor tied to wall time while the clocks ramp)
+__device__ __forceinline__ unsigned long long comm_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr unsigned long long kCommTimeoutNs = 4000000000ull;  // 4 s: a peer died; do not hang the GPU
+
 // true when every rank's flag of `flag_set` has reached `round` (false: timed out)
 __device__ __forceinline__ bool comm_wait_all(const CommTable &T, int rank, int world, int round,
                                               int flag_set, int *timed_out) {
@@ -72,9 +81,9 @@ __device__ __forceinline__ bool comm_wait_all(const CommTable &T, int rank, int 
   __syncthreads();
   if (threadIdx.x < world) {
     const int *f = T.flags[rank] + flag_set * kCommMaxWorld + threadIdx.x;
-    const long long t0 = clock64();
+    const unsigned long long t0 = comm_now_ns();
     while (ld_acquire_sys(f) < round) {
-      if (clock64() - t0 > 8000000000LL) {  // ~4 s: a peer died; do not hang the GPU
+      if (comm_now_ns() - t0 > kCommTimeoutNs) {
         *timed_out = 1;
         break;
       }
@@ -90,9 +99,10 @@ __device__ __forceinline__ int comm_row_len(int r, int D) { return (r < D) ? 7 *
 // A peer did not arrive: report it (flags[3], read by m3r_gn_iterations_done) and stop the solve --
 // with flags[0] set the linearisation, the factorisation and the retraction that are already
 // enqueued behind this kernel return at their first instruction, so Twc is not updated from a
-// stale or partly written system.  m3r_gn_begin clears both.
+// stale or partly written system.  m3r_gn_begin clears both.  EVERY CTA that times out reports (a
+// CTA that gave up has not written its rows, whatever CTA 0 saw).
 __device__ __forceinline__ void comm_fail(int *ws_flags) {
-  if (threadIdx.x == 0 && blockIdx.x == 0) {
+  if (threadIdx.x == 0) {
     ws_flags[3] = kGnErrExchangeTimeout;
     ws_flags[2] = 1;
     __threadfence();
@@ -304,17 +314,26 @@ extern "C" int m3r_gn_comm_signal(m3r_gn_comm *c, m3r_gn_workspace *ws, void *st
   return M3R_OK;
 }
 
-extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *out, int num_poses,
-                                  void *stream) {
+// true when m3r_gn_comm_reduce would take the reduce-scatter + all-gather form for this system
+static bool comm_two_phase(const m3r_gn_comm *c, int num_poses) {
+  const int forced = g_exchange_mode.load(std::memory_order_relaxed);  // m3r_debug_set_exchange_mode
+  return c->world > 1 &&
+         (forced == 2 || (forced == 0 && c->world >= 4 && m3r_gn_system_size(num_poses) >= (1 << 20)));
+}
+
+// phase: 0 = the whole reduce (the public entry point); 1 / 2 = its first / second half, for a host
+// that drives several ranks itself and orders the halves with events (gn_multi.cuh): in the
+// two-phase form 1 = reduce-scatter + signal, 2 = all-gather; in the one-shot form 1 = nothing,
+// 2 = the reduce.
+static int comm_reduce_phased(m3r_gn_comm *c, m3r_gn_workspace *ws, double *out, int num_poses,
+                              void *stream, int phase) {
   M3R_REQUIRE(c && ws && out, "gn_comm_reduce: null pointer");
   M3R_REQUIRE(c->connected && c->round > 0, "gn_comm_reduce: no round in progress");
   M3R_REQUIRE(num_poses >= 2 && m3r_gn_system_size(num_poses) <= c->cap,
               "gn_comm_reduce: system of %d poses exceeds the exchange area", num_poses);
   const int D = 7 * (num_poses - 1);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int forced = g_exchange_mode.load(std::memory_order_relaxed);  // m3r_debug_set_exchange_mode
-  const bool two_phase = forced == 2 || (forced == 0 && c->world >= 4 && m3r_gn_system_size(num_poses) >= (1 << 20));
-  if (two_phase && c->world > 1) {
+  if (comm_two_phase(c, num_poses)) {
     // rows split so that every rank reduces about the same number of elements
     m3r::CommSlices S{};
     long long total = D;  // the right-hand-side row
@@ -330,19 +349,29 @@ extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *
     S.begin[c->world] = D + 1;
     const int mine = S.begin[c->rank + 1] - S.begin[c->rank];
     const int rs_blocks = mine < m3r::kNumSMs * 4 ? (mine > 0 ? mine : 1) : m3r::kNumSMs * 4;
-    m3r::comm_reduce_scatter_kernel<<<rs_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, D,
-                                                             ws->flags);
-    M3R_LAUNCH_CHECK("comm_reduce_scatter_kernel");
-    m3r::comm_signal_kernel<<<1, 32, 0, s>>>(c->table, c->rank, c->world, c->round, 1);
-    M3R_LAUNCH_CHECK("comm_signal_kernel");
-    const int ag_blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
-    m3r::comm_gather_kernel<<<ag_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, out, D,
-                                                     ws->flags);
-    M3R_LAUNCH_CHECK("comm_gather_kernel");
+    if (phase != 2) {
+      m3r::comm_reduce_scatter_kernel<<<rs_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, D,
+                                                               ws->flags);
+      M3R_LAUNCH_CHECK("comm_reduce_scatter_kernel");
+      m3r::comm_signal_kernel<<<1, 32, 0, s>>>(c->table, c->rank, c->world, c->round, 1);
+      M3R_LAUNCH_CHECK("comm_signal_kernel");
+    }
+    if (phase != 1) {
+      const int ag_blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
+      m3r::comm_gather_kernel<<<ag_blocks, 256, 0, s>>>(c->table, S, c->rank, c->world, c->round, out, D,
+                                                       ws->flags);
+      M3R_LAUNCH_CHECK("comm_gather_kernel");
+    }
     return M3R_OK;
   }
+  if (phase == 1) return M3R_OK;
   const int blocks = D + 1 < m3r::kNumSMs * 8 ? D + 1 : m3r::kNumSMs * 8;
   m3r::comm_reduce_kernel<<<blocks, 256, 0, s>>>(c->table, c->rank, c->world, c->round, out, D, ws->flags);
   M3R_LAUNCH_CHECK("comm_reduce_kernel");
   return M3R_OK;
+}
+
+extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *out, int num_poses,
+                                  void *stream) {
+  return comm_reduce_phased(c, ws, out, num_poses, stream, 0);
 }

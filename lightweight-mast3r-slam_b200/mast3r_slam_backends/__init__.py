@@ -11,9 +11,15 @@ Differences from the reference that a caller can observe:
   * kernels run on torch's *current* stream, not the legacy default stream;
   * the Gauss-Newton calls never block the host (the reference synchronises three times per
     iteration, gn_kernels.cu:1199-1222); `Twc` is still updated in place and `[dx]` returned;
-  * dtype/device are validated (the reference only checks contiguity, gn.h:5).
+  * dtype/device are validated (the reference only checks contiguity, gn.h:5);
+  * with M3R_GN_DEVICES=G (or `set_gn_devices`) the same three Gauss-Newton calls spread the
+    directed edges over G GPUs of the box from this one process (m3r_gn_multi_*): the other
+    devices read the caller's tensors over NVLink peer access while they prepare their shard,
+    iterate on local memory and exchange the assembled systems over peer memory; `Twc` on the
+    caller's device is updated in place as before.
 """
 import ctypes
+import os
 import threading
 
 import torch
@@ -166,6 +172,116 @@ def release_workspaces():
     The caller must have synchronised the streams that used them."""
     with _ws_lock:
         _workspaces.clear()
+        _multis.clear()
+
+
+# ---- single-process multi-GPU (include/m3r_backends.h, m3r_gn_multi_*) -------------------------
+_gn_devices_override = None
+_multis = {}
+_last_multi = None
+
+
+def set_gn_devices(devices):
+    """Use several GPUs for the Gauss-Newton exports from this process.  `devices`: None (one
+    GPU), an int G (the caller's device and the next G-1), or an explicit list whose first entry
+    is the device the caller's tensors live on (an index may repeat: loop-back ranks on one
+    GPU), or "env" (default: follow the environment variable M3R_GN_DEVICES, which takes the same
+    forms, "4" or "0,1,2,3").  Anything but "env" overrides the environment variable."""
+    global _gn_devices_override
+    if isinstance(devices, str):
+        if devices != "env":
+            raise ValueError('set_gn_devices: expected None, an int, a list of device indices or "env"')
+        _gn_devices_override = None
+    else:
+        _gn_devices_override = devices if devices is not None else ()
+
+
+def _gn_device_list(dev):
+    spec = _gn_devices_override
+    if spec is None:
+        env = os.environ.get("M3R_GN_DEVICES", "").strip()
+        if not env:
+            return None
+        spec = [int(x) for x in env.split(",")] if "," in env else int(env)
+    if spec == () or spec is None:
+        return None
+    index = dev.index if dev.index is not None else torch.cuda.current_device()
+    if isinstance(spec, int):
+        if spec <= 1:
+            return None
+        count = torch.cuda.device_count()
+        if spec > count:
+            raise RuntimeError(f"M3R_GN_DEVICES={spec} but only {count} CUDA devices are visible")
+        ids = [(index + k) % count for k in range(spec)]
+    else:
+        ids = [int(x) for x in spec]
+        if len(ids) <= 1:
+            return None
+        if ids[0] != index:
+            raise RuntimeError(f"the first Gauss-Newton device ({ids[0]}) must be the tensors' device ({index})")
+    return ids
+
+
+class _Multi:
+    def __init__(self, ids):
+        self.ids = ids
+        self.handle = ctypes.c_void_p()
+        arr = (ctypes.c_int * len(ids))(*ids)
+        _lib.check(_lib.gn_multi_create(ctypes.byref(self.handle), arr, len(ids)), "gn_multi_create")
+
+    def __del__(self):
+        try:
+            if self.handle:
+                _lib.gn_multi_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def _multi(ids):
+    key = (tuple(ids), threading.get_ident(), torch.cuda.current_stream(ids[0]).cuda_stream)
+    with _ws_lock:
+        m = _multis.get(key)
+        if m is None:
+            m = _multis[key] = _Multi(ids)
+    return m
+
+
+def last_multi_report(Twc=None):
+    """After a multi-GPU Gauss-Newton call: {"devices", "begin_ms" per rank (for ranks > 0 the
+    scatter: remote reads + packing + compaction), "iterations", "replicas_bitwise_equal"}.
+    Synchronises every rank; for tests and benchmarks."""
+    m = _last_multi
+    if m is None:
+        return None
+    G = len(m.ids)
+    begin = (ctypes.c_float * G)()
+    iters, same = ctypes.c_int(0), ctypes.c_int(-1)
+    _lib.check(_lib.gn_multi_report(m.handle, _ptr(Twc) if Twc is not None else None,
+                                    Twc.shape[0] if Twc is not None else 0, begin, ctypes.byref(iters),
+                                    ctypes.byref(same) if Twc is not None else None), "gn_multi_report")
+    return {"devices": list(m.ids), "begin_ms": list(begin), "iterations": iters.value,
+            "replicas_bitwise_equal": bool(same.value) if Twc is not None else None}
+
+
+def _gn_multi_call(ids, kind, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, dx, N, n, E, max_iter,
+                   delta_thresh, K=None, **params):
+    global _last_multi
+    p = GnProblem()
+    p.kind = kind
+    p.num_poses, p.num_points, p.num_edges = N, n, E
+    p.edge_begin, p.edge_end = 0, E
+    p.Twc, p.Xs, p.Cs = Twc.data_ptr(), Xs.data_ptr(), Cs.data_ptr()
+    p.ii, p.jj = ii.data_ptr(), jj.data_ptr()
+    p.idx_ii2jj, p.valid_match, p.Q = idx_ii2jj.data_ptr(), valid_match.data_ptr(), Q.data_ptr()
+    p.K = K.data_ptr() if K is not None else None
+    for k, v in params.items():
+        setattr(p, k, v)
+    m = _multi(ids)
+    with torch.cuda.device(ids[0]):
+        rc = _lib.gn_multi_solve(m.handle, ctypes.byref(p), _ptr(dx), int(max_iter), float(delta_thresh),
+                                 _stream())
+    _lib.check(rc, "gn_multi_solve")
+    _last_multi = m
 
 
 def _gn_common_checks(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, extra=None):
@@ -197,6 +313,12 @@ def gauss_newton_rays(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_ray,
     dx = torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=dev)
     if N < 2 or max_iter <= 0:
         return [dx]
+    ids = _gn_device_list(dev)
+    if ids is not None:
+        _gn_multi_call(ids, _lib.GN_RAYS, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, dx, N, n, E, max_iter,
+                       delta_thresh, sigma_ray=float(sigma_ray), sigma_dist=float(sigma_dist),
+                       C_thresh=float(C_thresh), Q_thresh=float(Q_thresh))
+        return [dx]
     ws = _workspace(dev)
     with torch.cuda.device(dev):
         rc = _lib.gauss_newton_rays(
@@ -219,6 +341,13 @@ def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, height
     dx = torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=dev)
     if N < 2 or max_iter <= 0:
         return [dx]
+    ids = _gn_device_list(dev)
+    if ids is not None:
+        _gn_multi_call(ids, _lib.GN_CALIB, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, dx, N, n, E, max_iter,
+                       delta_thresh, K=K, height=int(height), width=int(width), pixel_border=int(pixel_border),
+                       z_eps=float(z_eps), sigma_pixel=float(sigma_pixel), sigma_depth=float(sigma_depth),
+                       C_thresh=float(C_thresh), Q_thresh=float(Q_thresh))
+        return [dx]
     ws = _workspace(dev)
     with torch.cuda.device(dev):
         rc = _lib.gauss_newton_calib(
@@ -237,6 +366,12 @@ def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_po
     dev, N, n, E = _gn_common_checks(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q)
     dx = torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=dev)
     if N < 2 or max_iter <= 0:
+        return [dx]
+    ids = _gn_device_list(dev)
+    if ids is not None:
+        _gn_multi_call(ids, _lib.GN_POINTS, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, dx, N, n, E, max_iter,
+                       delta_thresh, sigma_point=float(sigma_point), C_thresh=float(C_thresh),
+                       Q_thresh=float(Q_thresh))
         return [dx]
     ws = _workspace(dev)
     with torch.cuda.device(dev):

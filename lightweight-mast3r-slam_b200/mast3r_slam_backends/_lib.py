@@ -189,6 +189,16 @@ gn_comm_next_round = _sig("m3r_gn_comm_next_round", c_int, [c_void_p, ctypes.POI
 gn_comm_signal = _sig("m3r_gn_comm_signal", c_int, [c_void_p, c_void_p, c_void_p])
 gn_comm_reduce = _sig("m3r_gn_comm_reduce", c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p])
 debug_set_exchange_mode = _sig("m3r_debug_set_exchange_mode", None, [c_int])
+gn_multi_create = _sig("m3r_gn_multi_create", c_int, [ctypes.POINTER(c_void_p), ctypes.POINTER(c_int), c_int])
+gn_multi_destroy = _sig("m3r_gn_multi_destroy", None, [c_void_p])
+gn_multi_solve = _sig(
+    "m3r_gn_multi_solve", c_int, [c_void_p, ctypes.POINTER(GnProblem), c_void_p, c_int, c_float, c_void_p]
+)
+gn_multi_report = _sig(
+    "m3r_gn_multi_report",
+    c_int,
+    [c_void_p, c_void_p, c_int, ctypes.POINTER(c_float), ctypes.POINTER(c_int), ctypes.POINTER(c_int)],
+)
 
 # every symbol include/m3r_backends.h declares (checked by tests/test_abi.py)
 EXPORTS = [
@@ -227,6 +237,10 @@ EXPORTS = [
     "m3r_gn_comm_signal",
     "m3r_gn_comm_reduce",
     "m3r_debug_set_exchange_mode",
+    "m3r_gn_multi_create",
+    "m3r_gn_multi_destroy",
+    "m3r_gn_multi_solve",
+    "m3r_gn_multi_report",
 ]
 
 
