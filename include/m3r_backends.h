@@ -90,6 +90,25 @@ int m3r_refine_matches_v(const void *D11, const void *D21, const int64_t *p1, in
                          int b, int h, int w, int n, int fdim, int dtype, int radius,
                          int dilation_max, int variant, void *stream);
 
+/* Allocation-free variant of m3r_refine_matches.  It has NO counterpart in the reference: it was
+ * added for callers that cannot allocate (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments, same
+ * results (bit-exact), but the tile plan the kernel needs as scratch lives in one file-scope
+ * device array of fixed size inside the library, so the call performs no cudaMalloc /
+ * cudaMallocAsync / cudaFree and no other allocation.
+ *   limits: f16 descriptors with fdim 24, radius 3, one query per pixel (n = h*w), and at most
+ *           m3r_refine_matches_static_max_tiles() = 3200 query tiles of 16x16 per call
+ *           (b <= 4 frames at 512x384); anything else returns M3R_ERR_INVALID_ARGUMENT with a
+ *           message that names the limit;
+ *   cost:   every GPU that loads the library holds the 55 296-byte array until process exit;
+ *   sharing: all calls on a device share the array and it keeps the last call's contents
+ *           (nothing in it needs to start at zero); calls that overlap on the GPU -- different
+ *           streams, parallel graph branches -- race on it and must be serialised by the caller. */
+int m3r_refine_matches_static(const void *D11, const void *D21, const int64_t *p1, int64_t *p1_new,
+                              int b, int h, int w, int n, int fdim, int dtype, int radius,
+                              int dilation_max, void *stream);
+int64_t m3r_refine_matches_static_max_tiles(void);
+
 /* ---------------------------------------------------------------------------------------
  * Matching front end -- the torch code either side of the two kernels above, fused
  * (SURVEY.md 8f rows N1 and N3).

@@ -1147,6 +1147,102 @@ extern "C" int m3r_refine_matches_v(const void *D11, const void *D21, const int6
   return M3R_OK;
 }
 
+// -----------------------------------------------------------------------------------------
+// Allocation-free variant of the planned, tiled refine_matches (no counterpart in the
+// reference; added for callers that cannot allocate:
+// CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+//
+// The planned kernel needs scratch: one int4 box per query tile and one flag byte per tile
+// (padded to the 16-per-thread flag scan).  m3r_refine_matches takes it from a stream-ordered
+// pool; here it lives in ONE file-scope device array of fixed size, so the call allocates
+// nothing (no cudaMalloc / cudaMallocAsync / cudaFree, no torch allocation).  Consequences:
+//   * every GPU that loads the library holds the array (kRtStaticScratchBytes = 55 296 B)
+//     until the process exits;
+//   * at most kRtPlanUpTo = 3200 query tiles of 16x16 per call, i.e. b <= 4 frames at 512x384;
+//     larger problems are rejected with an error (use m3r_refine_matches);
+//   * all calls on a device share the array: calls that overlap on the GPU (different streams,
+//     or graph branches) race on it.  Serialise them.  Nothing in it has to start at zero: the
+//     plan pass writes boxes and flags of tiles [0, ntiles) before the main kernel reads them,
+//     and flag bytes beyond ntiles are masked by the scan, so the last call's contents are
+//     harmless.
+// In host code `g_rt_static_scratch` is only a stand-in for the symbol: the device address
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr size_t kRtStaticPlanBytes = static_cast<size_t>(kRtPlanUpTo) * sizeof(int4);
+constexpr size_t kRtStaticScratchBytes = kRtStaticPlanBytes + kRtMaxPlanned;
+static __device__ __align__(256) unsigned char g_rt_static_scratch[kRtStaticScratchBytes];
+
+static int rt_static_scratch_address(int dev, unsigned char **out) {
+  static unsigned char *addr[64] = {nullptr};
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lk(mu);
+  M3R_REQUIRE(dev >= 0 && dev < 64, "refine_matches_static: device index %d out of range", dev);
+  if (!addr[dev]) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_rt_static_scratch);  // `dev` is current (checked by the caller)
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_rt_static_scratch)");
+    addr[dev] = static_cast<unsigned char *>(p);
+  }
+  *out = addr[dev];
+  return M3R_OK;
+}
+
+extern "C" int64_t m3r_refine_matches_static_max_tiles(void) { return kRtPlanUpTo; }
+
+extern "C" int m3r_refine_matches_static(const void *D11, const void *D21, const int64_t *p1,
+                                         int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                         int dtype, int radius, int dilation_max, void *stream) {
+  M3R_REQUIRE(b >= 0 && n >= 0, "refine_matches_static: negative batch or point count");
+  if (b == 0 || n == 0) return M3R_OK;
+  M3R_REQUIRE(D11 && D21 && p1 && p1_new, "refine_matches_static: null pointer");
+  M3R_REQUIRE(h > 0 && w > 0, "refine_matches_static: bad shape");
+  M3R_REQUIRE(dtype == M3R_DTYPE_F16 && fdim == 24 && radius == 3 && dilation_max >= 1 && dilation_max <= 1024 &&
+                  static_cast<long long>(n) == static_cast<long long>(h) * w,
+              "refine_matches_static: only the tiled configuration is available without allocation "
+              "(f16 descriptors, fdim 24, radius 3, one query per pixel); use m3r_refine_matches");
+  M3R_REQUIRE(aligned16(D11) && aligned16(D21) && aligned16(p1) && aligned16(p1_new),
+              "refine_matches_static: D11, D21, p1, p1_new must be 16-byte aligned");
+  const int tiles_x = (w + kRtQ - 1) / kRtQ, tiles_y = (h + kRtQy - 1) / kRtQy;
+  const long long ntiles = static_cast<long long>(b) * tiles_x * tiles_y;
+  M3R_REQUIRE(ntiles <= kRtPlanUpTo,
+              "refine_matches_static: %lld query tiles of %dx%d exceed the static scratch (max %d tiles, "
+              "%zu bytes); use m3r_refine_matches",
+              ntiles, kRtQ, kRtQy, kRtPlanUpTo, kRtStaticScratchBytes);
+  int dev = 0;
+  M3R_CUDA_TRY(cudaGetDevice(&dev));
+  unsigned char *scratch = nullptr;
+  int rc = rt_static_scratch_address(dev, &scratch);
+  if (rc) return rc;
+  static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent (no allocation)
+  if (!attr_set_dev[dev & 63]) {
+    M3R_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tiled_kernel<true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, kRtSmemBytes));
+    attr_set_dev[dev & 63] = true;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int4 *plan = reinterpret_cast<int4 *>(scratch);
+  unsigned char *heavy = scratch + kRtStaticPlanBytes;
+  const int nt = static_cast<int>(ntiles);
+  const long long *p1l = reinterpret_cast<const long long *>(p1);
+  refine_plan_kernel<<<nt, kRtThreads, 0, s>>>(p1l, plan, heavy, h, w, dilation_max, tiles_x, tiles_y);
+  M3R_LAUNCH_CHECK("refine_plan_kernel");
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(nt), cfg.blockDim = dim3(kRtThreads), cfg.dynamicSmemBytes = kRtSmemBytes, cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = 1;
+  const int4 *plan_c = plan;
+  const unsigned char *heavy_c = heavy;
+  long long *lin_none = nullptr;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, refine_f16_tiled_kernel<true>, static_cast<const __half *>(D11),
+                                     static_cast<const __half *>(D21), p1l, reinterpret_cast<long long *>(p1_new),
+                                     lin_none, h, w, dilation_max, plan_c, heavy_c, tiles_x, tiles_y, nt);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  if (e != cudaSuccess) return cuda_fail(e, "refine_f16_tiled_kernel<planned, static scratch>");
+  return M3R_OK;
+}
+
 extern "C" int m3r_refine_matches(const void *D11, const void *D21, const int64_t *p1,
                                   int64_t *p1_new, int b, int h, int w, int n, int fdim,
                                   int dtype, int radius, int dilation_max, void *stream) {

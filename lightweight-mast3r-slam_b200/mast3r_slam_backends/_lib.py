@@ -119,6 +119,10 @@ refine_matches = _sig(
 refine_matches_v = _sig(
     "m3r_refine_matches_v", c_int, [c_void_p] * 4 + [c_int] * 9 + [c_void_p]
 )
+refine_matches_static = _sig(
+    "m3r_refine_matches_static", c_int, [c_void_p] * 4 + [c_int] * 8 + [c_void_p]
+)
+refine_matches_static_max_tiles = _sig("m3r_refine_matches_static_max_tiles", c_int64, [])
 prep_rays = _sig("m3r_prep_rays", c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p])
 match = _sig(
     "m3r_match",
@@ -209,6 +213,8 @@ EXPORTS = [
     "m3r_iter_proj_v",
     "m3r_refine_matches",
     "m3r_refine_matches_v",
+    "m3r_refine_matches_static",
+    "m3r_refine_matches_static_max_tiles",
     "m3r_prep_rays",
     "m3r_match",
     "m3r_match_confidence_scratch_bytes",
