@@ -85,6 +85,10 @@ def load(backend_module):
         mu = types.ModuleType("mast3r_slam.mast3r_utils")
         mu.resize_img = None
         mu.mast3r_match_symmetric = None  # set per scene, see SyntheticDecoder
+        # the reference modules bind `mast3r_slam_backends` at import (matching.py:5, global_opt.py:9);
+        # the name is registered only for the duration of those imports and restored afterwards, so
+        # that the rest of the test session keeps seeing the real package under that name
+        prev_backends = sys.modules.get("mast3r_slam_backends")
         sys.modules["mast3r_slam_backends"] = backend_module
         if root not in sys.path:
             sys.path.insert(0, root)
@@ -103,6 +107,10 @@ def load(backend_module):
         import mast3r_slam.global_opt as global_opt
         import mast3r_slam.matching as matching
 
+        if prev_backends is not None:
+            sys.modules["mast3r_slam_backends"] = prev_backends
+        else:
+            del sys.modules["mast3r_slam_backends"]
         _loaded.update(cfg=cfg, frame=frame, global_opt=global_opt, matching=matching, mu=mu)
     ns = types.SimpleNamespace(**_loaded)
     ns.matching.mast3r_slam_backends = backend_module
