@@ -621,7 +621,64 @@ def gn_parity(be, g, D, kind, Twc_sharded, rank, world, refmod):
     return out
 
 
-def gn_report(be, g, D, kind, rank, world, peak, refmod, reps=3, nccl_too=True, single_call=True):
+_sp_seq = [0]
+
+
+def time_gn_single_process(be, g, D, kind, rank, local_rank, world, Twc_spmd, reps=3):
+    """The same graph through the UNCHANGED drop-in call from ONE process (rank 0) that drives all
+    `world` devices (m3r_gn_multi_*, M3R_GN_DEVICES): what global_opt.py:142-143 would get.  The
+    other ranks wait on the host (c10d store: no kernel on their GPUs), keeping their memory.
+    `scatter_ms` is the per-call preparation of the non-primary devices: reading the caller's
+    Xs / Cs and their shard's idx / valid / Q rows over NVLink + packing + compaction; it is paid on
+    every call (the callers' tensors are re-stacked every solve, global_opt.py:114-121) and is
+    inside `ms_per_iter`."""
+    import datetime
+
+    store = torch.distributed.distributed_c10d._get_default_store()
+    _sp_seq[0] += 1
+    key = f"m3r_single_process_done_{_sp_seq[0]}"
+    torch.cuda.synchronize()
+    barrier(world)
+    out = None
+    if rank == 0:
+        try:
+            be.set_gn_devices([(local_rank + k) % world for k in range(world)])
+            calls = []
+            for rep in range(reps + 1):  # the first call also allocates and enables peer access
+                Twc = g["Twc_init"].clone()
+                torch.cuda.synchronize()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+                GN_CALLS[kind](be, g, D, Twc, 10)
+                t1.record()
+                torch.cuda.synchronize()
+                r = be.last_multi_report(Twc)
+                calls.append((t0.elapsed_time(t1), r, Twc))
+            ms, r, Twc = min(calls[1:], key=lambda c: c[0])
+            out = {"mode": f"one process, {world} devices (M3R_GN_DEVICES), caller's tensors on device {local_rank}",
+                   "value": 10 / (ms * 1e-3), "unit": "iters/s", "ms_per_iter": ms / 10,
+                   "first_call_ms": calls[0][0], "steady_call_ms": ms,
+                   "scatter_ms": {"first_call_max_over_devices": max(calls[0][1]["begin_ms"][1:]),
+                                  "steady_max_over_devices": max(r["begin_ms"][1:]),
+                                  "steady_per_device": [round(x, 4) for x in r["begin_ms"]],
+                                  "primary_begin_ms": r["begin_ms"][0]},
+                   "iters_done": r["iterations"], "replicas_bitwise_equal": r["replicas_bitwise_equal"],
+                   "max_abs_diff_vs_spmd": (Twc - Twc_spmd).abs().max().item(),
+                   "stat": f"smallest of {reps} calls after the first"}
+        except Exception as exc:  # report, do not lose the line
+            out = {"error": str(exc)[:300]}
+        finally:
+            be.set_gn_devices(None)
+            be.release_workspaces()
+            store.set(key, "1")
+    else:
+        store.wait([key], datetime.timedelta(seconds=600))
+    barrier(world)
+    return out
+
+
+def gn_report(be, g, D, kind, rank, world, peak, refmod, reps=3, nccl_too=True, single_call=True,
+              single_process=False, local_rank=0):
     """One GN configuration: phase times (smallest-total repetition of `reps`), roofline of the
     linearisation, parity fields, and at N > 1 the NCCL variant beside the peer-memory one."""
     from mast3r_slam_backends import _lib
@@ -658,6 +715,9 @@ def gn_report(be, g, D, kind, rank, world, peak, refmod, reps=3, nccl_too=True, 
     if world == 1 and single_call:
         ms_call, _ = time_gn_single_call(be, g, D, kind)
         out["single_call_ms_per_iter"] = ms_call / 10
+    out["mode"] = "one process per GPU (torchrun), edges sharded over the ranks" if world > 1 else "one GPU"
+    if world > 1 and single_process:
+        out["single_process"] = time_gn_single_process(be, g, D, kind, rank, local_rank, world, gr["Twc"])
     return out
 
 
@@ -962,7 +1022,8 @@ def main():
         if args.profile:
             torch.cuda.synchronize()
             torch.cuda.profiler.start()
-        line["gn"] = gn_report(be, g, D, args.gn_kind, rank, world, peak, refmod, reps=1 if args.profile else 3)
+        line["gn"] = gn_report(be, g, D, args.gn_kind, rank, world, peak, refmod, reps=1 if args.profile else 3,
+                               single_process=not args.profile, local_rank=local_rank)
         if args.profile:
             torch.cuda.profiler.stop()
         if not (args.profile or args.skip_gn_configs):
@@ -986,7 +1047,7 @@ def main():
             # configs[4]: 256-keyframe loop-closure graph, gauss_newton_points, D = 1785
             g256 = make_gn_graph(256, "cuda", seed=0)
             cfgs["points256"] = gn_report(be, g256, D, "points", rank, world, peak, refmod, reps=2,
-                                          single_call=False)
+                                          single_call=False, single_process=True, local_rank=local_rank)
             del g256
             torch.cuda.empty_cache()
             line["gn_configs"] = cfgs

@@ -170,9 +170,11 @@ def _workspace(device):
 def release_workspaces():
     """Free every cached Gauss-Newton workspace (device scratch grows to the largest graph seen).
     The caller must have synchronised the streams that used them."""
+    global _last_multi
     with _ws_lock:
         _workspaces.clear()
         _multis.clear()
+        _last_multi = None
 
 
 # ---- single-process multi-GPU (include/m3r_backends.h, m3r_gn_multi_*) -------------------------
