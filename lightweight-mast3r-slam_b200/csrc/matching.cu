@@ -42,7 +42,7 @@ __device__ __forceinline__ float clampf(float x, float lo, float hi) {
 
 // One LM evaluation at (u,v): interpolated ray (normalised), gradients, cost.
 template <bool kWithGrad, typename Fetch>
-__device__ __forceinline__ void eval_at(Fetch fetch, float u, float v, const float pt[3],
+__device__ __forceinline__ void eval_at(const Fetch &fetch, float u, float v, const float pt[3],
                                         float gx[3], float gy[3], float err[3], float &cost) {
   const int u11 = static_cast<int>(floorf(u));
   const int v11 = static_cast<int>(floorf(v));
@@ -54,10 +54,8 @@ __device__ __forceinline__ void eval_at(Fetch fetch, float u, float v, const flo
   const float w22 = (1.0f - du) * (1.0f - dv);
   constexpr int NC = kWithGrad ? 9 : 3;
   float r11[NC], r12[NC], r21[NC], r22[NC];
-  fetch(u11 + 1, v11 + 1, r11);  // weighted by w11 (:167)
-  fetch(u11, v11 + 1, r12);
-  fetch(u11 + 1, v11, r21);
-  fetch(u11, v11, r22);
+  // r11 = texel (u11+1, v11+1), weighted by w11 (:167); r12 = (u11, v11+1); r21 = (u11+1, v11); r22 = (u11, v11)
+  fetch.template quad<NC>(u11, v11, r11, r12, r21, r22);
   float r[3];
 #pragma unroll
   for (int j = 0; j < 3; j++) r[j] = w11 * r11[j] + w12 * r12[j] + w21 * r21[j] + w22 * r22[j];
@@ -90,6 +88,55 @@ struct GlobalFetch {
 #pragma unroll
     for (int c = 0; c < NC; c++) out[c] = __ldg(s + c);
   }
+  template <int NC>
+  __device__ __forceinline__ void quad(int u11, int v11, float *r11, float *r12, float *r21, float *r22) const {
+    operator()<NC>(u11 + 1, v11 + 1, r11);
+    operator()<NC>(u11, v11 + 1, r12);
+    operator()<NC>(u11 + 1, v11, r21);
+    operator()<NC>(u11, v11, r22);
+  }
+};
+
+// The same [h,w,9] API image read with 128-bit loads.  The two texels (u, u+1) a bilinear footprint
+// takes from one image row are 18 consecutive floats starting at word 9t (t = texel index in the
+// whole tensor).  9t mod 4 = t mod 4 =: s, so they lie inside the 16-byte-aligned words
+// [9t - s, 9t - s + 21): five aligned float4 plus, when s = 3, one more word.  A footprint is then
+// 10 LDG.128 (+ 2 predicated LDG.32) instead of 36 LDG.32 -- and, what the kernel is really bound
+// by, a third of the L1 wavefronts: lanes of a warp sit 36 bytes apart, so EVERY load instruction
+// of the warp touches 9-10 cache lines whatever its width.  The 18 values are moved into place with
+// two rounds of selects on the bits of s (no local memory, no divergence).  Values are the same
+// bits as the scalar path.
+// Preconditions (checked on the host, else the scalar path runs): the tensor is 16-byte aligned and
+// holds a multiple of 4 floats, so an aligned chunk that starts inside it ends inside it.
+struct VecFetch {
+  const float4 *img4;  // the whole [b,h,w,9] tensor
+  size_t base_texel;   // b * h * w
+  int w;
+  __device__ __forceinline__ void row(int u, int v, float *L, float *R) const {
+    const size_t t = base_texel + static_cast<size_t>(v) * w + u;
+    const unsigned s = static_cast<unsigned>(t) & 3u;
+    const float4 *p = img4 + ((9 * t - s) >> 2);
+    const float4 c0 = __ldg(p), c1 = __ldg(p + 1), c2 = __ldg(p + 2), c3 = __ldg(p + 3), c4 = __ldg(p + 4);
+    float x20 = 0.0f;
+    if (s == 3u) x20 = __ldg(reinterpret_cast<const float *>(p + 5));  // word 9t + 17: last one of texel u+1
+    const float W[21] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w, c2.x, c2.y, c2.z,
+                         c2.w, c3.x, c3.y, c3.z, c3.w, c4.x, c4.y, c4.z, c4.w, x20};
+    const bool s1 = (s & 1u) != 0, s2 = (s & 2u) != 0;
+    float A[20];
+#pragma unroll
+    for (int i = 0; i < 20; i++) A[i] = s1 ? W[i + 1] : W[i];
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+      L[i] = s2 ? A[i + 2] : A[i];
+      R[i] = s2 ? A[i + 11] : A[i + 9];
+    }
+  }
+  template <int NC>
+  __device__ __forceinline__ void quad(int u11, int v11, float *r11, float *r12, float *r21, float *r22) const {
+    static_assert(NC == 9, "the vector path fetches whole texels");
+    row(u11, v11, r22, r21);
+    row(u11, v11 + 1, r12, r11);
+  }
 };
 
 // The same gather from the padded image the fused front end writes for itself (48-byte texels:
@@ -107,6 +154,13 @@ struct PaddedFetch {
       const float4 c = __ldg(s + 2);
       out[3] = a.w, out[4] = b.x, out[5] = b.y, out[6] = b.z, out[7] = b.w, out[8] = c.x;
     }
+  }
+  template <int NC>
+  __device__ __forceinline__ void quad(int u11, int v11, float *r11, float *r12, float *r21, float *r22) const {
+    operator()<NC>(u11 + 1, v11 + 1, r11);
+    operator()<NC>(u11, v11 + 1, r12);
+    operator()<NC>(u11 + 1, v11, r21);
+    operator()<NC>(u11, v11, r22);
   }
 };
 
@@ -130,16 +184,25 @@ __device__ __forceinline__ void lm_step(const float gx[3], const float gy[3], co
 
 // The memoised LM loop (MODE 0 of iter_proj_kernel, see below), shared with the fused match
 // kernel.
+#ifdef M3R_IP_COUNT  // experiments: number of fetched evaluations and the last iteration that fetched
+__device__ int g_ip_evals, g_ip_last;
+#define IP_COUNT(it_) (n_evals++, last_fetch = (it_))
+#else
+#define IP_COUNT(it_) ((void)0)
+#endif
 template <typename Fetch>
 __device__ __forceinline__ void iter_proj_memo(const Fetch &fetch, const float pt[3], float &u,
                                                float &v, float u_hi, float v_hi, int max_iter,
-                                               float lambda_init, float cost_thresh, bool &conv) {
-  auto f9 = [&](int uu, int vv, float *out) { fetch.template operator()<9>(uu, vv, out); };
+                                               float lambda_init, float cost_thresh, bool &conv,
+                                               int *stats = nullptr) {
+#ifdef M3R_IP_COUNT
+  int n_evals = 1, last_fetch = -1;
+#endif
   float lambda = lambda_init;
   conv = false;
   if (max_iter <= 0) return;
   float gx[3], gy[3], err[3], cost;
-  eval_at<true>(f9, u, v, pt, gx, gy, err, cost);
+  eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
   float ut = 0.f, vt = 0.f, cost_t = 0.f;  // last rejected trial since the pixel last moved
   bool have_trial = false;
   for (int it = 0; it < max_iter; it++) {
@@ -152,8 +215,9 @@ __device__ __forceinline__ void iter_proj_memo(const Fetch &fetch, const float p
     } else if (have_trial && u_new == ut && v_new == vt) {
       new_cost = cost_t;
     } else {
-      eval_at<true>(f9, u_new, v_new, pt, ngx, ngy, nerr, new_cost);
+      eval_at<true>(fetch, u_new, v_new, pt, ngx, ngy, nerr, new_cost);
       fresh = true;
+      IP_COUNT(it);
     }
     // a memoised cost is never below `cost` (it was rejected against the same `cost`)
     if (fresh && new_cost < cost) {
@@ -171,9 +235,19 @@ __device__ __forceinline__ void iter_proj_memo(const Fetch &fetch, const float p
       conv = cost < cost_thresh;
     }
   }
+#ifdef M3R_IP_COUNT
+  if (stats) stats[0] = n_evals, stats[1] = last_fetch;
+#endif
 }
 
-constexpr int kIpThreads = 128;
+#ifndef M3R_IP_THREADS
+#define M3R_IP_THREADS 128
+#endif
+#ifndef M3R_IP_MINCTAS
+#define M3R_IP_MINCTAS 1
+#endif
+constexpr int kIpThreads = M3R_IP_THREADS;
+constexpr int kIpMinCtas = M3R_IP_MINCTAS;  // register cap of iter_proj_kernel through __launch_bounds__
 
 // MODE 1: every iteration evaluates the current pixel (9 channels) and the trial pixel
 // (3 channels), as the reference kernel does: two gathers per iteration.
@@ -188,7 +262,7 @@ constexpr int kIpThreads = 128;
 // coordinate and the remaining iterations touch no memory.  At most one gather per iteration,
 // typically 3-4 per point instead of 20; results are bit-identical to MODE 1.
 template <int MODE>
-__global__ void __launch_bounds__(kIpThreads)
+__global__ void __launch_bounds__(kIpThreads, kIpMinCtas)
     iter_proj_kernel(const float *__restrict__ rays, const float *__restrict__ pts,
                      const float *__restrict__ p_init, float *__restrict__ p_new,
                      uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,
@@ -198,8 +272,6 @@ __global__ void __launch_bounds__(kIpThreads)
   if (idx >= n) return;
   const size_t gi = static_cast<size_t>(b) * n + idx;
   const GlobalFetch fetch{rays + static_cast<size_t>(b) * h * w * 9, w};
-  auto f9 = [&](int uu, int vv, float *out) { fetch.template operator()<9>(uu, vv, out); };
-  auto f3 = [&](int uu, int vv, float *out) { fetch.template operator()<3>(uu, vv, out); };
 
   const float2 p0 = __ldg(reinterpret_cast<const float2 *>(p_init) + gi);
   const float pt[3] = {__ldg(pts + gi * 3 + 0), __ldg(pts + gi * 3 + 1), __ldg(pts + gi * 3 + 2)};
@@ -212,11 +284,11 @@ __global__ void __launch_bounds__(kIpThreads)
   if (MODE == 1) {
     for (int it = 0; it < max_iter; it++) {
       float gx[3], gy[3], err[3], cost;
-      eval_at<true>(f9, u, v, pt, gx, gy, err, cost);
+      eval_at<true>(fetch, u, v, pt, gx, gy, err, cost);
       float u_new, v_new;
       lm_step(gx, gy, err, lambda, u, v, u_hi, v_hi, u_new, v_new);
       float err2[3], new_cost;  // cost at the trial pixel, ray channels only (:225-256)
-      eval_at<false>(f3, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
+      eval_at<false>(fetch, u_new, v_new, pt, nullptr, nullptr, err2, new_cost);
       if (new_cost < cost) {  // accept (:259-264)
         u = u_new;
         v = v_new;
@@ -227,6 +299,17 @@ __global__ void __launch_bounds__(kIpThreads)
         conv = cost < cost_thresh;
       }
     }
+  } else if (MODE == 2) {  // memoised, 128-bit loads (host checked the alignment preconditions)
+    const VecFetch vfetch{reinterpret_cast<const float4 *>(rays), static_cast<size_t>(b) * h * w, w};
+#ifdef M3R_IP_COUNT
+    int st[2] = {0, 0};
+    iter_proj_memo(vfetch, pt, u, v, u_hi, v_hi, max_iter, lambda_init, cost_thresh, conv, st);
+    reinterpret_cast<float2 *>(p_new)[gi] = make_float2(u, v);
+    converged[gi] = static_cast<uint8_t>((conv ? 1 : 0) | (st[0] << 1) | ((st[1] + 1) << 5));  // evals <= 11, last+1 <= 10
+    return;
+#else
+    iter_proj_memo(vfetch, pt, u, v, u_hi, v_hi, max_iter, lambda_init, cost_thresh, conv);
+#endif
   } else {
     iter_proj_memo(fetch, pt, u, v, u_hi, v_hi, max_iter, lambda_init, cost_thresh, conv);
   }
@@ -1074,9 +1157,17 @@ extern "C" int m3r_iter_proj_v(const float *rays, const float *pts, const float 
   if (variant == 1) {
     iter_proj_kernel<1><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
                                                max_iter, lambda_init, cost_thresh);
-  } else if (variant == 0) {
-    iter_proj_kernel<0><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
-                                               max_iter, lambda_init, cost_thresh);
+  } else if (variant == 0 || variant == 2) {
+    // variant 0: memoised LM with 128-bit loads when the image allows it (16-byte aligned, a
+    // multiple of 4 floats: true for every contiguous torch tensor whose b*h*w is a multiple of 4);
+    // variant 2: the same with scalar loads (what variant 0 falls back to)
+    const bool vec = variant == 0 && aligned16(rays) && ((static_cast<long long>(b) * h * w) & 3LL) == 0;
+    if (vec)
+      iter_proj_kernel<2><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
+                                                 max_iter, lambda_init, cost_thresh);
+    else
+      iter_proj_kernel<0><<<grid, block, 0, s>>>(rays, pts, p_init, p_new, converged, h, w, n,
+                                                 max_iter, lambda_init, cost_thresh);
   } else {
     set_error("iter_proj: unknown variant %d", variant);
     return M3R_ERR_INVALID_ARGUMENT;
