@@ -205,6 +205,12 @@ def time_matching(be, sets, M, steps, warmup, world, per_kernel=True):
     torch.cuda.synchronize()
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if not per_kernel:
+        # The device idles ~1 ms in FRONT of the start event while the host enqueues the first steps:
+        # the timed region (between the two events, on the device) then starts with work queued, as
+        # in a streaming caller, instead of exposing the host's first launches -- with 8 ranks on one
+        # box a single descheduled rank otherwise sets the max over ranks of a 3 ms region.
+        torch.cuda._sleep(2_000_000)
     t0.record()
     for i in range(steps):
         s = sets[i % len(sets)]
@@ -971,6 +977,9 @@ def main():
         "config": {"workload": WORKLOAD,
                    "replicas": "matching runs as independent replicas per GPU (b = 1 does not shard, SURVEY 8e)",
                    "l2": f"inputs rotated over {NUM_SETS} frame sets ({NUM_SETS}x38 MB > 126 MB L2)",
+                   "timing": "CUDA events on the launching stream around all K steps, max over ranks; a ~1 ms "
+                             "device-side sleep is enqueued in front of the start event so that the region "
+                             "starts with the host ahead of the device (no host launch latency inside it)",
                    "params": M},
         "clocks": clocks,
         "per_rank_ms_per_step": {"min": min(rank_ms), "median": statistics.median(rank_ms), "max": max(rank_ms)},

@@ -38,6 +38,7 @@ struct ClSmem {
   double yk[kPB];
   double bl[2][kPB];   // right-hand side entries of the owned rows
   int bad;
+  int prog;  // written by warp_chol32, unused here
   int pad_;
   double blk[kClBlkDoubles];
 };
@@ -100,7 +101,7 @@ __global__ void __cluster_dims__(kClSize, 1, 1) __launch_bounds__(kClThreads, 1)
       double a[kPB];
 #pragma unroll
       for (int cc = 0; cc < kPB; cc++) a[cc] = (cc <= lane) ? blkk[lane * ld + k * kPB + cc] : 0.0;
-      warp_chol32(a, lane, S.stage[0][0], S.dinv, &S.bad);
+      warp_chol32(a, lane, S.stage[0][0], S.dinv, &S.bad, S.L11, &S.prog);  // (this variant ignores the per-pivot counter)
 #pragma unroll
       for (int cc = 0; cc < kPB; cc++) {
         S.L11[lane][cc] = (cc <= lane) ? a[cc] : 0.0;

@@ -105,11 +105,19 @@ __device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
 // with a[c] -= (a[j]/d) * A[c][j].  (A 64-bit __shfl_sync costs ~12 SASS instructions; the
 // shuffle version of this routine was 8k instructions and the kernel 300 KB, far beyond the
 // instruction cache, which made every panel run at cold-cache speed.)
+// After pivot j the warp publishes column j of L (L11[.][j]; zeros above the diagonal) and 1/L_jj,
+// then raises *prog to j + 1: the TRSM warps, the y_k chain and (one panel later) the inverse of the
+// block follow the factorisation one pivot behind instead of starting when all 32 pivots are done
+// (the TRSM alone was 3.6 us per panel behind the POTRF, profiles/r1_i_coop_solver_phases.txt).
 __device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *col, double *dinv,
-                                            int *bad) {
+                                            int *bad, double (*L11)[kPB + 1], volatile int *prog) {
 #pragma unroll
   for (int j = 0; j < kPB; j++) {
-    __syncwarp();  // previous readers of col are done
+    // one barrier does two jobs: the previous readers of col are done, and every lane's part of
+    // column j-1 (written at the end of the previous round) precedes the counter that lets the
+    // followers read it.  All lanes store the same value: no divergent branch on the chain.
+    __syncwarp();
+    if (j > 0) *prog = j;
     col[lane] = a[j];
     __syncwarp();
     const double d = col[j];
@@ -127,10 +135,24 @@ __device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *col
     const double tj = a[j] * rc;  // A[lane][j] / d
 #pragma unroll
     for (int c = j + 1; c < kPB; c++) a[c] -= tj * col[c];  // meaningful for lanes >= c
-    if (lane == 0) dinv[j] = r;
-    a[j] *= r;  // lane j: sqrt(d); lanes > j: L[lane][j]
+    dinv[j] = r;  // every lane holds the same r
+    a[j] *= r;    // lane j: sqrt(d); lanes > j: L[lane][j]
+    L11[lane][j] = (lane >= j) ? a[j] : 0.0;
   }
+  __syncwarp();
+  *prog = kPB;
 }
+
+// follower side: block until pivot c of this panel's POTRF is published
+// (Called once per group of pivots, with a back-off: every poll is a shared-memory load in the
+// pipe the POTRF chain's own stores and loads go through; polling every pivot from four warps cost
+// the chain 15 %.)
+__device__ __forceinline__ void wait_pivot(volatile int *prog, int c) {
+  while (*prog <= c) __nanosleep(100);
+  __threadfence_block();
+}
+constexpr int kFollowGroup = 4;  // TRSM rows and y_k follow the POTRF in groups of this many pivots
+constexpr int kInvGroup = 8;     // the block inverse (off the critical path) in groups of this many
 
 template <int TILE>  // 32 or 64: A22 tile (tr, tc) -= L21[tr] L21[tc]^T
 __device__ __forceinline__ void coop_update_tile(double *__restrict__ A, int D, int k0, int pb,
@@ -180,6 +202,30 @@ __device__ __forceinline__ void tile_from_index(int tile, int &tr, int &tc) {
   tc = tile - tr * (tr + 1) / 2;
 }
 
+// M = L^-1 of one factored 32x32 diagonal block (by one warp, lane = column of M), stored row-major
+// with the reciprocal pivots behind it: the layout the backward phase reads from `ldiag`.
+__device__ __forceinline__ void coop_invert_block(double (*L)[kPB + 1], const double *dinv_blk,
+                                                  double *__restrict__ Ld, int lane, volatile int *prog) {
+  // lane c solves L m = e_c, right-looking: once m_k is known every later row takes its update,
+  // so a pivot costs two dependent operations (the chain of a left-looking dot product grows with
+  // the row: 9 us per block), and step k needs column k of L only -- the warp follows the POTRF of
+  // the same panel one pivot behind, like the TRSM rows
+  double acc[kPB];
+#pragma unroll
+  for (int r = 0; r < kPB; r++) acc[r] = (r == lane) ? 1.0 : 0.0;
+#pragma unroll
+  for (int k = 0; k < kPB; k++) {
+    if ((k % kInvGroup) == 0) wait_pivot(prog, k + kInvGroup - 1);
+    const double mk = acc[k] * dinv_blk[k];
+    acc[k] = mk;
+#pragma unroll
+    for (int r = k + 1; r < kPB; r++) acc[r] -= L[r][k] * mk;
+  }
+#pragma unroll
+  for (int r = 0; r < kPB; r++) Ld[r * kPB + lane] = acc[r];
+  Ld[kPB * kPB + lane] = dinv_blk[lane];
+}
+
 constexpr int kLs = kPB + 2;  // even leading dimension: 16-byte aligned pairs for LDS.128
 struct CoopSmem {
   double L11[kPB][kPB + 1];
@@ -197,6 +243,7 @@ struct CoopSmem {
     } b;
   } u;
   int bad;
+  int prog;  // pivots of the current panel's POTRF that are published (warp_chol32)
 };
 constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
 
@@ -249,9 +296,9 @@ __global__ void __launch_bounds__(kCoopThreads)
 #endif
       const int row0 = k0 + pb + rc * kTrsmRows;
       const int nrows = max(0, min(kTrsmRows, D - row0));
-      // named barrier 1 ("L11 ready"): warp 0 arrives; the TRSM warps, the y_k warp and, on the
-      // CTA that keeps the diagonal blocks for the backward phase, the inverse warp wait
-      const int bar1 = 64 + 32 * kTrsmWarps + ((rc == 0) ? 32 : 0);
+      double (*L11)[kPB + 1] = S.L11;
+      double *dinv = S.dinv;
+      volatile int *prog = &S.prog;  // pivots of this panel's POTRF published so far
       // 1. what the POTRF needs (diagonal block, the previous panel's rows of it, rhs) by all
       //    threads; the CTA's 128 panel rows are loaded by the TRSM warps themselves AFTER this
       //    barrier, beside the diagonal-block update and the POTRF instead of in front of them
@@ -265,6 +312,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         S.Ls[r][c] = (la && r < pb) ? A[g + kp + c] : 0.0;
       }
       if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
+      if (t == 0) S.prog = 0;  // no pivot of this panel is published yet
       __syncthreads();
       COOP_ATICK(8);
 #ifdef M3R_COOP_PROF
@@ -285,6 +333,11 @@ __global__ void __launch_bounds__(kCoopThreads)
         if (trsm_warp) asm volatile("bar.sync 4, 128;");  // rows staged
         else asm volatile("bar.arrive 4, 128;");
       }
+      if (warp == 3 && rc == 0) {
+        // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot products
+        //    instead of a 32-pivot chain), on a warp that is idle once the rows are staged
+        coop_invert_block(L11, dinv, ldiag + static_cast<size_t>(k0 / kPB) * kLdStride, lane, prog);
+      }
       // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
       //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
       //    272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner
@@ -292,14 +345,16 @@ __global__ void __launch_bounds__(kCoopThreads)
       //    garbage and are never read.  (The first version gave every thread 4 outputs of one
       //    row: 5 shared loads per 4 DFMA, 4.2 us per panel on the critical path.)
       if (la && diag_warp) {
-        double acc[4][4];
+        // two accumulators per output (even and odd columns of Ls): the dependent DFMA chain is
+        // what this step costs (fp64 latency, not issue), and it halves
+        double acc[4][4], acc1[4][4];
         const int u = ((warp == 0) ? 0 : (warp == 4) ? 1 : (warp == 5) ? 2 : 3) * 32 + lane;
         const int tile = u & 63, half = u >> 6;
         const int tr = tile >> 3, tc = tile & 7;
 #pragma unroll
         for (int i = 0; i < 4; i++)
 #pragma unroll
-          for (int k = 0; k < 4; k++) acc[i][k] = 0.0;
+          for (int k = 0; k < 4; k++) acc[i][k] = 0.0, acc1[i][k] = 0.0;
 #pragma unroll 4
         for (int j = half * (kPB / 2); j < (half + 1) * (kPB / 2); j += 2) {
           double2 av[4], bv[4];
@@ -311,8 +366,15 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int k = 0; k < 4; k++) acc[i][k] = fma(av[i].y, bv[k].y, fma(av[i].x, bv[k].x, acc[i][k]));
+            for (int k = 0; k < 4; k++) {
+              acc[i][k] = fma(av[i].x, bv[k].x, acc[i][k]);
+              acc1[i][k] = fma(av[i].y, bv[k].y, acc1[i][k]);
+            }
         }
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int k = 0; k < 4; k++) acc[i][k] += acc1[i][k];
         if (half == 1) {
 #pragma unroll
           for (int i = 0; i < 4; i++)
@@ -335,11 +397,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         double a[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++) a[c] = (c <= lane) ? S.Ad[lane][c] : 0.0;
-        warp_chol32(a, lane, S.col, S.dinv, &bad);
-#pragma unroll
-        for (int c = 0; c < kPB; c++) S.L11[lane][c] = (c <= lane) ? a[c] : 0.0;
-        __syncwarp();
-        asm volatile("bar.arrive 1, %0;" ::"r"(bar1));  // L11, dinv ready
+        warp_chol32(a, lane, S.col, dinv, &bad, L11, prog);  // publishes L11 / dinv pivot by pivot
         COOP_ATICK(10);
       } else if (trsm_warp) {
         // 4. this thread's row: fold in the previous panel's update while warp 0 factors
@@ -362,15 +420,16 @@ __global__ void __launch_bounds__(kCoopThreads)
         }
         COOP_TTICK(0);
         const double rhs_old = has_row ? rhs[row] : 0.0;  // in flight during the TRSM
-        asm volatile("bar.sync 1, %0;" ::"r"(bar1));
         COOP_TTICK(1);
-        // right-looking TRSM: independent updates per column -> ILP
+        // right-looking TRSM: independent updates per column -> ILP.  Column c of L11 is final
+        // once pivot c is published, so the row follows the POTRF one pivot behind.
 #pragma unroll
         for (int c = 0; c < kPB; c++) {
-          const double xc = x[c] * S.dinv[c];
+          if ((c % kFollowGroup) == 0) wait_pivot(prog, c + kFollowGroup - 1);
+          const double xc = x[c] * dinv[c];
           x[c] = xc;
 #pragma unroll
-          for (int k = c + 1; k < kPB; k++) x[k] -= xc * S.L11[k][c];
+          for (int k = c + 1; k < kPB; k++) x[k] -= xc * L11[k][c];
         }
         if (has_row) {
           double *Ar = A + static_cast<size_t>(row) * D + k0;
@@ -391,43 +450,20 @@ __global__ void __launch_bounds__(kCoopThreads)
         }
         COOP_TTICK(3);
       } else if (warp == 5) {
-        // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp
-        asm volatile("bar.sync 1, %0;" ::"r"(bar1));
-        double a[kPB];
-#pragma unroll
-        for (int c = 0; c < kPB; c++) a[c] = S.L11[lane][c];
+        // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp and one pivot
+        //    behind it: step c needs L11[.][c] and dinv[c] only
         double mine = S.bk[lane];
 #pragma unroll
         for (int c = 0; c < kPB; c++) {  // y_c travels through shared memory (see warp_chol32)
-          if (lane == c) mine *= S.dinv[c], yk[c] = mine;
+          if ((c % kFollowGroup) == 0) wait_pivot(prog, c + kFollowGroup - 1);
+          if (lane == c) mine *= dinv[c], yk[c] = mine;
           __syncwarp();
-          if (lane > c) mine -= a[c] * yk[c];
+          if (lane > c) mine -= L11[lane][c] * yk[c];
         }
         __syncwarp();
         if (lane >= pb) yk[lane] = 0.0;
         asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));
         if (rc == 0 && lane < pb) xbuf[k0 + lane] = mine;
-      } else if (warp == 4 && rc == 0) {
-        // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot
-        //    products instead of a 32-pivot chain).  Lane c builds column c of M row by row:
-        //    M[r][c] = (delta_rc - sum_{k<r} L11[r][k] M[k][c]) / L11[r][r].  Runs beside the
-        //    TRSM of this panel, off the critical path.
-        asm volatile("bar.sync 1, %0;" ::"r"(bar1));
-        double mcol[kPB];
-#pragma unroll
-        for (int r = 0; r < kPB; r++) {
-          double s0 = (r == lane) ? 1.0 : 0.0, s1 = 0.0;
-#pragma unroll
-          for (int k = 0; k < r; k++) {
-            if (k & 1) s1 -= S.L11[r][k] * mcol[k];
-            else s0 -= S.L11[r][k] * mcol[k];
-          }
-          mcol[r] = (s0 + s1) * S.dinv[r];
-        }
-        double *Ld = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
-#pragma unroll
-        for (int r = 0; r < kPB; r++) Ld[r * kPB + lane] = mcol[r];
-        Ld[kPB * kPB + lane] = S.dinv[lane];
       }
       __syncthreads();
       COOP_ATICK(13);
