@@ -392,6 +392,16 @@ int m3r_gn_comm_signal(m3r_gn_comm *comm, m3r_gn_workspace *ws, void *stream);
  * the summed system, i.e. everything m3r_gn_solve_retract reads. */
 int m3r_gn_comm_reduce(m3r_gn_comm *comm, m3r_gn_workspace *ws, double *out, int num_poses,
                        void *stream);
+/* m3r_gn_comm_reduce in two halves, for a host thread that drives SEVERAL ranks itself (ranks that
+ * share a process: m3r_gn_multi_*, the loop-back tests).  Such a host must not rely on the reduce
+ * kernels' spin-wait: a kernel that waits for a flag is only safe when the kernel that sets it is
+ * guaranteed to run beside it, which CUDA does not promise for two streams of one device, nor when
+ * the setter has not been enqueued yet.  Instead it enqueues, for every rank, signal -> [event],
+ * then phase 1 behind the events of all ranks -> [event], then phase 2 behind those, so that every
+ * wait finds its flags set.  phase 1: reduce-scatter + second signal (nothing in the one-shot form);
+ * phase 2: all-gather (the whole reduce in the one-shot form). */
+int m3r_gn_comm_reduce_phase(m3r_gn_comm *comm, m3r_gn_workspace *ws, double *out, int num_poses,
+                             int phase, void *stream);
 /* Exchange algorithm of m3r_gn_comm_reduce: 0 = chosen by size (one-shot below 8 MB or fewer
  * than 4 ranks, else reduce-scatter + all-gather), 1 = always one-shot, 2 = always two-phase.
  * Process-wide; for tests and benchmarks. */

@@ -375,3 +375,9 @@ extern "C" int m3r_gn_comm_reduce(m3r_gn_comm *c, m3r_gn_workspace *ws, double *
                                   void *stream) {
   return comm_reduce_phased(c, ws, out, num_poses, stream, 0);
 }
+
+extern "C" int m3r_gn_comm_reduce_phase(m3r_gn_comm *c, m3r_gn_workspace *ws, double *out, int num_poses,
+                                        int phase, void *stream) {
+  M3R_REQUIRE(phase == 1 || phase == 2, "gn_comm_reduce_phase: phase must be 1 or 2 (got %d)", phase);
+  return comm_reduce_phased(c, ws, out, num_poses, stream, phase);
+}

@@ -192,6 +192,9 @@ gn_comm_connect_local = _sig("m3r_gn_comm_connect_local", c_int, [ctypes.POINTER
 gn_comm_next_round = _sig("m3r_gn_comm_next_round", c_int, [c_void_p, ctypes.POINTER(c_void_p)])
 gn_comm_signal = _sig("m3r_gn_comm_signal", c_int, [c_void_p, c_void_p, c_void_p])
 gn_comm_reduce = _sig("m3r_gn_comm_reduce", c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p])
+gn_comm_reduce_phase = _sig(
+    "m3r_gn_comm_reduce_phase", c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]
+)
 debug_set_exchange_mode = _sig("m3r_debug_set_exchange_mode", None, [c_int])
 gn_multi_create = _sig("m3r_gn_multi_create", c_int, [ctypes.POINTER(c_void_p), ctypes.POINTER(c_int), c_int])
 gn_multi_destroy = _sig("m3r_gn_multi_destroy", None, [c_void_p])
@@ -242,6 +245,7 @@ EXPORTS = [
     "m3r_gn_comm_next_round",
     "m3r_gn_comm_signal",
     "m3r_gn_comm_reduce",
+    "m3r_gn_comm_reduce_phase",
     "m3r_debug_set_exchange_mode",
     "m3r_gn_multi_create",
     "m3r_gn_multi_destroy",

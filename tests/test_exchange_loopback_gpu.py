@@ -5,10 +5,13 @@ round parities and reduction orders are exactly those of the N-GPU run; only the
 missing.  This is what the driver's 1-GPU lease can execute; tests/test_multigpu_gpu.py runs
 the same protocol over NVLink when two GPUs are visible.
 
-Deadlock freedom on one device: every rank's signal is enqueued before any rank's reduce, and
-neither the waiting reduce kernels (at most D + 1 CTAs of 256 threads) nor the cooperative
-solve need the whole machine, so a spinning kernel never keeps the kernel it waits for from
-being scheduled."""
+Forward progress on one device: CUDA does not guarantee that kernels of two streams of ONE device
+run side by side, so a reduce kernel must never have to spin for a flag here.  The host (one thread
+drives all ranks) therefore orders the streams with events exactly as m3r_gn_multi_solve does:
+signal -> event; phase 1 of the reduce behind every rank's event -> event; phase 2 behind those
+(m3r_gn_comm_reduce_phase).  The flag protocol itself still runs in every kernel and is what the
+assertions check; the spin path is exercised where ranks own their device (tests/test_multigpu_gpu.py,
+bench.py under torchrun)."""
 import ctypes
 
 import pytest
@@ -26,6 +29,7 @@ class _Rank:
         from mast3r_slam_backends.staged import StagedGN, shard_range
 
         self.stream = torch.cuda.Stream()
+        self.ev_sig, self.ev_p1 = torch.cuda.Event(), torch.cuda.Event()
         b0, b1 = shard_range(g["E"], rank, world)
         t = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in g.items()}
         self.Twc = t["Twc_init"].clone()
@@ -72,9 +76,17 @@ def _solve(ranks, iters, delta_thresh, delay_rank=None):
                 r.stage.linearize(into=buf.value)
         for r in ranks:
             _lib.check(_lib.gn_comm_signal(r.comm, r.stage.ws.handle, r.sptr()), "signal")
-        for r in ranks:
-            _lib.check(_lib.gn_comm_reduce(r.comm, r.stage.ws.handle, ctypes.c_void_p(r.stage.system.data_ptr()),
-                                           r.stage.N, r.sptr()), "reduce")
+            r.ev_sig.record(r.stream)
+        for phase, before, after in ((1, "ev_sig", "ev_p1"), (2, "ev_p1", None)):
+            for r in ranks:
+                for q in ranks:
+                    if q is not r:
+                        r.stream.wait_event(getattr(q, before))
+                _lib.check(_lib.gn_comm_reduce_phase(r.comm, r.stage.ws.handle,
+                                                     ctypes.c_void_p(r.stage.system.data_ptr()), r.stage.N, phase,
+                                                     r.sptr()), "reduce_phase")
+                if after:
+                    getattr(r, after).record(r.stream)
         for r in ranks:
             with torch.cuda.stream(r.stream):
                 r.stage.solve_retract(delta_thresh)
