@@ -549,21 +549,77 @@ __global__ void __launch_bounds__(64)
 // ----------------------------------------------------------------------------------------
 constexpr int kAsmMaxStagedEdges = 4096;  // (io, jo) pairs staged in shared memory: 32 KB
 
+// Which 7x7 blocks of the lower triangle receive anything from this shard's edges does not change
+// over the iterations of a call: m3r_gn_begin marks them (gn_mark_blocks_kernel) and lists them in
+// row-major order (gn_list_blocks_kernel).  Per iteration the system is zeroed with one memset and
+// only the listed blocks get a CTA.  (One CTA per block of the whole NB x NB grid, each staging all
+// edge pairs, was 24 us per iteration at 64 keyframes and 65 025 CTAs x 16 KB of L2 reads at 256;
+// a 64-keyframe graph touches 309 of its 3 969 blocks.)
+__global__ void gn_mark_blocks_kernel(const int *__restrict__ pose_i, const int *__restrict__ pose_j,
+                                      int edge_begin, int num_shard_edges, int NB,
+                                      unsigned char *__restrict__ blk_flag) {
+  const int le = blockIdx.x * blockDim.x + threadIdx.x;
+  if (le >= num_shard_edges) return;
+  const int io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;  // -1: the fixed pose
+  if (io >= 0) blk_flag[static_cast<size_t>(io) * NB + io] = 1;
+  if (jo >= 0) blk_flag[static_cast<size_t>(jo) * NB + jo] = 1;
+  if (io >= 0 && jo >= 0 && io != jo) blk_flag[static_cast<size_t>(max(io, jo)) * NB + min(io, jo)] = 1;
+}
+
+constexpr int kListThreads = 1024;
+__global__ void __launch_bounds__(kListThreads)
+    gn_list_blocks_kernel(const unsigned char *__restrict__ blk_flag, int NB, int2 *__restrict__ blk_list,
+                          int *__restrict__ blk_count, int capacity) {
+  // ordered compaction of the NB * NB flags by one CTA: thread t owns a contiguous range
+  __shared__ int warp_tot[kListThreads / 32];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int total = NB * NB;
+  const int per = (total + kListThreads - 1) / kListThreads;
+  const int k0 = min(t * per, total), k1 = min(k0 + per, total);
+  int mine = 0;
+  for (int k = k0; k < k1; k++) mine += blk_flag[k] != 0;
+  int incl = mine;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += o;
+  }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  if (t < 32) {
+    int w = warp_tot[t];
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, w, off);
+      if (t >= off) w += o;
+    }
+    warp_tot[t] = w;
+  }
+  __syncthreads();
+  int pos = incl - mine + (warp > 0 ? warp_tot[warp - 1] : 0);
+  for (int k = k0; k < k1; k++) {
+    if (blk_flag[k] != 0) {
+      if (pos < capacity) blk_list[pos] = make_int2(k / NB, k % NB);  // (block row a, block col b), a >= b
+      pos++;
+    }
+  }
+  if (t == kListThreads - 1) *blk_count = min(pos, capacity);
+}
+
 template <bool STAGED>
 __global__ void __launch_bounds__(64)
     gn_assemble_kernel(const double *__restrict__ edge_H, const double *__restrict__ edge_g,
                        const int *__restrict__ pose_i, const int *__restrict__ pose_j,
                        int edge_begin, int num_shard_edges, int NB, double *__restrict__ sys,
-                       const int *__restrict__ flags) {
+                       const int *__restrict__ flags, const int2 *__restrict__ blk_list,
+                       const int *__restrict__ blk_count) {
   if (flags[0]) return;
-  const int a = blockIdx.y, b = blockIdx.x;  // block row, block col
+  if (static_cast<int>(blockIdx.x) >= *blk_count) return;  // the grid is an upper bound (edges + poses)
+  const int2 ab = blk_list[blockIdx.x];
+  const int a = ab.x, b = ab.y;  // block row, block col (a >= b); everything else was zeroed by the memset
   const int t = threadIdx.x;
   const int D = NB * 7;
   const int r = t / 7, c = t % 7;
-  if (a < b) {  // strictly upper blocks are never read; keep them zero for the all-reduce
-    if (t < 49) sys[static_cast<size_t>(a * 7 + r) * D + (b * 7 + c)] = 0.0;
-    return;
-  }
   // the shard's (pose_i, pose_j) pairs: one coalesced pass into shared memory, so that the scan
   // below costs shared-memory latency per 64-edge tile instead of an L2 round trip
   extern __shared__ int2 ep[];
@@ -572,45 +628,17 @@ __global__ void __launch_bounds__(64)
       ep[e] = make_int2(pose_i[edge_begin + e] - 1, pose_j[edge_begin + e] - 1);
     __syncthreads();
   }
-  __shared__ int hit[64];
-  __shared__ int nhit;
-  __shared__ unsigned masks[2];
+  // Two passes: the scan over the shard's edges only appends the edges that touch this block to a
+  // list in shared memory (edge order preserved); their 7x7 blocks are fetched afterwards, eight per
+  // round with the loads of a round issued together and the adds in list order.  (Fetching per
+  // 64-edge tile made every tile with a hit wait for its own L2 round trip: 22 us per launch at 64
+  // keyframes for whichever block had the longest chain.)
+  constexpr int kHitCap = 1024;
+  __shared__ int hit[kHitCap];
+  __shared__ unsigned masks[2][2];  // double-buffered by tile parity: one barrier per tile
   double accH = 0.0, accg = 0.0;
-  for (int e0 = 0; e0 < num_shard_edges; e0 += 64) {
-    const int le = e0 + t;
-    int code = 0;  // 1: +H (diag, i side)  2: +H (diag, j side)  3: -H (off-diagonal)
-    if (le < num_shard_edges) {
-      int io, jo;
-      if (STAGED) io = ep[le].x, jo = ep[le].y;
-      else io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;
-      if (a == b) {
-        if (io == a && jo == a) code = 0;  // self edge: the four blocks cancel exactly
-        else if (io == a) code = 1;
-        else if (jo == a) code = 2;
-      } else if ((io == a && jo == b) || (io == b && jo == a)) {
-        code = 3;
-      }
-    }
-    // compact the hits of this tile in edge order
-    const unsigned m0 = __ballot_sync(0xffffffffu, code != 0);
-    if ((t & 31) == 0) masks[t >> 5] = m0;
-    __syncthreads();
-    const unsigned lo = masks[0], hi = masks[1];
-    if ((lo | hi) == 0u) {  // no edge of this tile touches the block (the common case)
-      __syncthreads();
-      continue;
-    }
-    if (code != 0) {
-      const int pos = (t < 32) ? __popc(lo & ((1u << t) - 1u))
-                               : __popc(lo) + __popc(hi & ((1u << (t - 32)) - 1u));
-      hit[pos] = (le << 2) | code;
-    }
-    if (t == 0) nhit = __popc(lo) + __popc(hi);
-    __syncthreads();
-    const int nh = nhit;
-    // eight hits per round: the loads of a round are independent and issued together (a
-    // diagonal block of a well connected keyframe collects dozens of edges; one L2 round trip
-    // per edge was the whole cost of this kernel), the adds keep the edge order
+  auto flush = [&](int nh) {
+    __syncthreads();  // the list is complete
     constexpr int kHitUnroll = 8;
     for (int k0 = 0; k0 < nh; k0 += kHitUnroll) {
       double v[kHitUnroll];
@@ -636,8 +664,42 @@ __global__ void __launch_bounds__(64)
         }
       }
     }
+    __syncthreads();  // the list may be overwritten
+  };
+  int nh = 0;  // uniform over the CTA
+  for (int e0 = 0, tile = 0; e0 < num_shard_edges; e0 += 64, tile++) {
+    const int le = e0 + t;
+    int code = 0;  // 1: +H (diag, i side)  2: +H (diag, j side)  3: -H (off-diagonal)
+    if (le < num_shard_edges) {
+      int io, jo;
+      if (STAGED) io = ep[le].x, jo = ep[le].y;
+      else io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;
+      if (a == b) {
+        if (io == a && jo == a) code = 0;  // self edge: the four blocks cancel exactly
+        else if (io == a) code = 1;
+        else if (jo == a) code = 2;
+      } else if ((io == a && jo == b) || (io == b && jo == a)) {
+        code = 3;
+      }
+    }
+    const unsigned m0 = __ballot_sync(0xffffffffu, code != 0);
+    if ((t & 31) == 0) masks[tile & 1][t >> 5] = m0;
     __syncthreads();
+    const unsigned lo = masks[tile & 1][0], hi = masks[tile & 1][1];
+    const int cnt = __popc(lo) + __popc(hi);
+    if (cnt == 0) continue;  // no edge of this tile touches the block (the common case)
+    if (nh + cnt > kHitCap) {  // uniform: the list is full (a pose with > 1000 edges in this shard)
+      flush(nh);
+      nh = 0;
+    }
+    if (code != 0) {
+      const int pos = (t < 32) ? __popc(lo & ((1u << t) - 1u))
+                               : __popc(lo) + __popc(hi & ((1u << (t - 32)) - 1u));
+      hit[nh + pos] = (le << 2) | code;
+    }
+    nh += cnt;
   }
+  flush(nh);
   if (t < 49) sys[static_cast<size_t>(a * 7 + r) * D + (b * 7 + c)] = accH;
   else if (t < 56 && a == b) sys[static_cast<size_t>(D) * D + a * 7 + (t - 49)] = accg;
 }
@@ -1172,10 +1234,12 @@ struct m3r_gn_workspace {
   DevBuf<double> partials;        // [items, 35]
   DevBuf<double> edge_H, edge_g;  // [E_shard, 49], [E_shard, 7]
   DevBuf<double> system;          // D*D + D (single-GPU entry points)
+  DevBuf<unsigned char> blk_flag; // [NB * NB] 7x7 blocks of the lower triangle this shard's edges touch
+  DevBuf<int2> blk_list;          // their (row, col), row-major order; the count lives in flags[5]
   DevBuf<double> ldiag;           // factored diagonal blocks of the Cholesky
   DevBuf<double> xbuf;            // [D]
   int *flags = nullptr;           // [0] done, [1] iterations, [2] factorisation failed, [3] error code
-                                  // (kGnErr*), [4] id remap took the general path
+                                  // (kGnErr*), [4] id remap took the general path, [5] non-empty blocks
   int begun_edges = -1;
   int begun_shard_begin = -1, begun_shard_end = -1, begun_points = -1;
 };
@@ -1201,6 +1265,7 @@ extern "C" void m3r_gn_workspace_destroy(m3r_gn_workspace *ws) {
   if (!ws) return;
   ws->pose_i.release(), ws->pose_j.release(), ws->first.release(), ws->partials.release();
   ws->cs_copy.release();
+  ws->blk_flag.release(), ws->blk_list.release();
   ws->packed.release(), ws->ck.release(), ws->cidx.release(), ws->cq.release(), ws->counts.release();
   ws->edge_H.release(), ws->edge_g.release(), ws->system.release(), ws->ldiag.release();
   ws->xbuf.release();
@@ -1260,9 +1325,24 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
     M3R_LAUNCH_CHECK("gn_rank_kernel");
   }
 
-  // per-call preparation: packed keyframes, compacted match lists of this shard
   const int n = prob->num_points;
   const int ES = prob->edge_end - prob->edge_begin;
+  {  // the 7x7 blocks this shard's edges touch (gn_assemble_kernel)
+    const int NB = prob->num_poses - 1;
+    const size_t nblk = static_cast<size_t>(NB) * NB;
+    const int cap = ES + NB;  // an edge adds at most one off-diagonal block; NB diagonal blocks
+    if ((rc = ws->blk_flag.reserve(nblk))) return rc;
+    if ((rc = ws->blk_list.reserve(static_cast<size_t>(cap)))) return rc;
+    M3R_CUDA_TRY(cudaMemsetAsync(ws->blk_flag.p, 0, nblk, s));
+    if (ES > 0) {
+      gn_mark_blocks_kernel<<<(ES + 255) / 256, 256, 0, s>>>(ws->pose_i.p, ws->pose_j.p, prob->edge_begin, ES, NB,
+                                                             ws->blk_flag.p);
+      M3R_LAUNCH_CHECK("gn_mark_blocks_kernel");
+    }
+    gn_list_blocks_kernel<<<1, kListThreads, 0, s>>>(ws->blk_flag.p, NB, ws->blk_list.p, ws->flags + 5, cap);
+    M3R_LAUNCH_CHECK("gn_list_blocks_kernel");
+  }
+  // per-call preparation: packed keyframes, compacted match lists of this shard
   const int chunks = (n + kChunk - 1) / kChunk;
   const size_t items = static_cast<size_t>(ES) * chunks;
   M3R_REQUIRE(items * kAccWarps < (1ull << 31), "gn_begin: shard too large (%zu items)", items);
@@ -1394,13 +1474,18 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
     M3R_LAUNCH_CHECK("gn_edge_finalize_kernel");
   }
   const int NB = prob->num_poses - 1;
+  // zero the whole system (also what the exchange and the solver expect of blocks nobody writes),
+  // then one CTA per block that has edges; ES + NB bounds their number
+  M3R_CUDA_TRY(cudaMemsetAsync(system, 0, static_cast<size_t>(m3r_gn_system_size(prob->num_poses)) * sizeof(double), s));
+  const int asm_grid = ES + NB;
   if (ES <= kAsmMaxStagedEdges)
-    gn_assemble_kernel<true><<<dim3(NB, NB), 64, static_cast<size_t>(ES) * sizeof(int2), s>>>(
-        ws->edge_H.p, ws->edge_g.p, ws->pose_i.p, ws->pose_j.p, prob->edge_begin, ES, NB, system, ws->flags);
+    gn_assemble_kernel<true><<<asm_grid, 64, static_cast<size_t>(ES) * sizeof(int2), s>>>(
+        ws->edge_H.p, ws->edge_g.p, ws->pose_i.p, ws->pose_j.p, prob->edge_begin, ES, NB, system, ws->flags,
+        ws->blk_list.p, ws->flags + 5);
   else
-    gn_assemble_kernel<false><<<dim3(NB, NB), 64, 0, s>>>(ws->edge_H.p, ws->edge_g.p, ws->pose_i.p,
-                                                        ws->pose_j.p, prob->edge_begin, ES, NB, system,
-                                                        ws->flags);
+    gn_assemble_kernel<false><<<asm_grid, 64, 0, s>>>(ws->edge_H.p, ws->edge_g.p, ws->pose_i.p, ws->pose_j.p,
+                                                     prob->edge_begin, ES, NB, system, ws->flags, ws->blk_list.p,
+                                                     ws->flags + 5);
   M3R_LAUNCH_CHECK("gn_assemble_kernel");
   return M3R_OK;
 }
