@@ -866,18 +866,30 @@ def host_us_per_call(be, s, M, g16, D, calls=40):
 
 
 def host_topology():
+    """NUMA / PCIe facts of the host that the e2e figures depend on (all ranks share them)."""
     try:
         nodes = open("/sys/devices/system/node/online").read().strip()
     except Exception:
         nodes = "?"
+    aff = []
     try:
         topo = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
-        rows = [ln for ln in topo.splitlines() if ln.startswith("GPU")]
-        aff = sorted({ln.split("\t")[-3].strip() + "/numa " + ln.split("\t")[-2].strip() for ln in rows if "\t" in ln})
+        lines = [ln for ln in topo.splitlines() if ln.strip()]
+        hdr = [h.strip() for h in lines[0].split("\t")]
+        for ln in lines[1:]:
+            f = [x.strip() for x in ln.split("\t")]
+            if f and f[0].startswith("GPU") and len(f) >= len(hdr):
+                row = dict(zip(hdr, f[1:])) if hdr and not hdr[0] else dict(zip(hdr[1:], f[1:]))
+                aff.append({"gpu": f[0], "cpu_affinity": row.get("CPU Affinity"), "numa": row.get("NUMA Affinity")})
     except Exception:
-        aff = []
+        pass
+    try:
+        link = subprocess.run(["nvidia-smi", "--query-gpu=pcie.link.gen.current,pcie.link.width.current",
+                               "--format=csv,noheader", "-i", "0"], capture_output=True, text=True, timeout=20).stdout.strip()
+    except Exception:
+        link = None
     return {"numa_nodes_online": nodes, "host_cores_visible": len(os.sched_getaffinity(0)),
-            "gpu_cpu_affinity": aff[:8]}
+            "gpu_cpu_affinity": aff[:8], "pcie_gen_width_gpu0": link}
 
 
 def gather_list(x, world):

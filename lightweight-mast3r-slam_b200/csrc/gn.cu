@@ -297,7 +297,10 @@ __global__ void __launch_bounds__(kAccThreads) gn_compact_kernel(const CompactAr
     const size_t slot = (static_cast<size_t>(item) * kAccWarps + warp) * kSeg;
     const int k_begin = ch * kChunk + warp * kSeg;
     int fill = 0;
-    constexpr int U = 4;  // rounds in flight: the kernel is a latency-bound stream + gather
+#ifndef M3R_COMPACT_U
+#define M3R_COMPACT_U 4
+#endif
+    constexpr int U = M3R_COMPACT_U;  // rounds in flight: the kernel is a latency-bound stream + gather
     for (int r0 = 0; r0 < kSeg / 32; r0 += U) {
       float q[U], cj[U];
       long long raw[U];
