@@ -257,11 +257,19 @@ constexpr int kChunk = kSeg * kAccWarps;    // points per work item (one CTA pas
 
 __global__ void __launch_bounds__(256)
     gn_pack_kernel(const float *__restrict__ Xs, const float *__restrict__ Cs,
-                   float4 *__restrict__ P, float *__restrict__ cs_copy, size_t total) {
+                   float4 *__restrict__ P, float *__restrict__ cs_copy, size_t total, int n,
+                   const unsigned char *__restrict__ kf_needed) {
   // cs_copy: local copy of Cs for the compaction's gathers when Xs / Cs live on another device
-  // (single-process multi-GPU, gn_multi.cuh); null otherwise
-  for (size_t k = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < total;
-       k += static_cast<size_t>(gridDim.x) * blockDim.x) {
+  // (single-process multi-GPU, gn_multi.cuh); null otherwise.  kf_needed: keyframes that an edge
+  // of this shard touches; the others are never gathered and are skipped (on 8 ranks a shard of a
+  // 64-keyframe graph touches about a third of them: less HBM traffic, and in the single-process
+  // mode less NVLink traffic out of the caller's device, which is what bounds its scatter).
+  // grid: (chunks of a keyframe's points, keyframes)
+  const int kf = blockIdx.y;
+  if (!kf_needed[kf]) return;
+  const size_t base = static_cast<size_t>(kf) * n;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    const size_t k = base + p;
     const float c = __ldcs(Cs + k);
     P[k] = make_float4(__ldcs(Xs + 3 * k), __ldcs(Xs + 3 * k + 1), __ldcs(Xs + 3 * k + 2), c);
     if (cs_copy) cs_copy[k] = c;
@@ -560,9 +568,12 @@ constexpr int kAsmMaxStagedEdges = 4096;  // (io, jo) pairs staged in shared mem
 // a 64-keyframe graph touches 309 of its 3 969 blocks.)
 __global__ void gn_mark_blocks_kernel(const int *__restrict__ pose_i, const int *__restrict__ pose_j,
                                       int edge_begin, int num_shard_edges, int NB,
-                                      unsigned char *__restrict__ blk_flag) {
+                                      unsigned char *__restrict__ blk_flag,
+                                      unsigned char *__restrict__ kf_needed) {
   const int le = blockIdx.x * blockDim.x + threadIdx.x;
   if (le >= num_shard_edges) return;
+  kf_needed[pose_i[edge_begin + le]] = 1;  // keyframes whose points this shard gathers (gn_pack_kernel)
+  kf_needed[pose_j[edge_begin + le]] = 1;
   const int io = pose_i[edge_begin + le] - 1, jo = pose_j[edge_begin + le] - 1;  // -1: the fixed pose
   if (io >= 0) blk_flag[static_cast<size_t>(io) * NB + io] = 1;
   if (jo >= 0) blk_flag[static_cast<size_t>(jo) * NB + jo] = 1;
@@ -1237,6 +1248,7 @@ struct m3r_gn_workspace {
   DevBuf<double> partials;        // [items, 35]
   DevBuf<double> edge_H, edge_g;  // [E_shard, 49], [E_shard, 7]
   DevBuf<double> system;          // D*D + D (single-GPU entry points)
+  DevBuf<unsigned char> kf_needed; // [N] keyframes this shard's edges touch
   DevBuf<unsigned char> blk_flag; // [NB * NB] 7x7 blocks of the lower triangle this shard's edges touch
   DevBuf<int2> blk_list;          // their (row, col), row-major order; the count lives in flags[5]
   DevBuf<double> ldiag;           // factored diagonal blocks of the Cholesky
@@ -1268,7 +1280,7 @@ extern "C" void m3r_gn_workspace_destroy(m3r_gn_workspace *ws) {
   if (!ws) return;
   ws->pose_i.release(), ws->pose_j.release(), ws->first.release(), ws->partials.release();
   ws->cs_copy.release();
-  ws->blk_flag.release(), ws->blk_list.release();
+  ws->blk_flag.release(), ws->blk_list.release(), ws->kf_needed.release();
   ws->packed.release(), ws->ck.release(), ws->cidx.release(), ws->cq.release(), ws->counts.release();
   ws->edge_H.release(), ws->edge_g.release(), ws->system.release(), ws->ldiag.release();
   ws->xbuf.release();
@@ -1336,10 +1348,12 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
     const int cap = ES + NB;  // an edge adds at most one off-diagonal block; NB diagonal blocks
     if ((rc = ws->blk_flag.reserve(nblk))) return rc;
     if ((rc = ws->blk_list.reserve(static_cast<size_t>(cap)))) return rc;
+    if ((rc = ws->kf_needed.reserve(static_cast<size_t>(prob->num_poses)))) return rc;
     M3R_CUDA_TRY(cudaMemsetAsync(ws->blk_flag.p, 0, nblk, s));
+    M3R_CUDA_TRY(cudaMemsetAsync(ws->kf_needed.p, 0, static_cast<size_t>(prob->num_poses), s));
     if (ES > 0) {
       gn_mark_blocks_kernel<<<(ES + 255) / 256, 256, 0, s>>>(ws->pose_i.p, ws->pose_j.p, prob->edge_begin, ES, NB,
-                                                             ws->blk_flag.p);
+                                                             ws->blk_flag.p, ws->kf_needed.p);
       M3R_LAUNCH_CHECK("gn_mark_blocks_kernel");
     }
     gn_list_blocks_kernel<<<1, kListThreads, 0, s>>>(ws->blk_flag.p, NB, ws->blk_list.p, ws->flags + 5, cap);
@@ -1371,10 +1385,11 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
     if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride))) return rc;
   }
   {
-    const size_t want_blocks = (total + 255) / 256;
-    const size_t cap = static_cast<size_t>(kNumSMs) * 16;
-    gn_pack_kernel<<<static_cast<int>(want_blocks < cap ? want_blocks : cap), 256, 0, s>>>(
-        prob->Xs, prob->Cs, ws->packed.p, ws->copy_cs ? ws->cs_copy.p : nullptr, total);
+    // 4 points per thread in flight; keyframes in grid.y (at most 512 keyframe slots, frame.py:221)
+    M3R_REQUIRE(prob->num_poses <= 65535, "gn_begin: %d poses exceed grid.y", prob->num_poses);
+    const int chunks = (n + 1023) / 1024;
+    gn_pack_kernel<<<dim3(chunks, prob->num_poses), 256, 0, s>>>(
+        prob->Xs, prob->Cs, ws->packed.p, ws->copy_cs ? ws->cs_copy.p : nullptr, total, n, ws->kf_needed.p);
     M3R_LAUNCH_CHECK("gn_pack_kernel");
   }
   if (items > 0) {
