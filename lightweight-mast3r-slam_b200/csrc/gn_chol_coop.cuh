@@ -98,6 +98,75 @@ __device__ __forceinline__ double chain_rcp(double d) {
 // out-of-line so that the pivot chain's code stays small (never taken for sane systems)
 __device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
 
+// ---- factorisation of the 32x32 diagonal block: one warp runs the elimination chain, another scales
+//
+// Measured (tools/ubench_potrf.cu, ubench_potrf2.cu; profiles/r2_i_potrf_chain.md): the 32-pivot loop
+// is executed by ONE in-order warp, so every dependent instruction it carries is latency the next
+// pivot waits for, whether or not it is on the mathematical critical path.  The loop that did
+// everything (reciprocal, square root, column scaling, the d <= 0 / wide-range branches) took 404
+// cycles per pivot alone on an SM, 316 without the branches, and 155 when it carries the chain only.
+//
+// warp_chol32_chain (warp 0): lane r holds row r of the block in registers.  Pivot j needs ONE update
+// of pivot j - 1 (column j of every row); that update is done first, the unscaled column j goes to
+// U[j][lane] at once, and the other row updates of pivot j - 1 issue beside the reciprocal of pivot j.
+// Straight-line code: no branch on the pivot value (an unusable pivot is replaced by 1 and
+// remembered), and no __syncwarp inside the loop -- here it would be a BRA.DIV, which ends a basic
+// block and with it everything ptxas can overlap.  The warp is brought together once in front of
+// the loop; straight-line code cannot diverge, and the LSU handles one warp's shared-memory
+// instructions in order, so a store by lane a is visible to the load by lane b that follows it in
+// program order.  WARP_FENCE keeps the compiler from reordering them.
+// *prog_u = number of complete columns of U (U[c][c] is the pivot d_c).
+#define M3R_WARP_FENCE() asm volatile("" ::: "memory")
+__device__ __forceinline__ bool warp_chol32_chain(double a[kPB], int lane, double (*U)[kPB],
+                                                  volatile int *prog_u) {
+  __syncwarp();
+  U[0][lane] = a[0];
+  M3R_WARP_FENCE();
+  *prog_u = 1;
+  double d = U[0][0];
+  bool abn = false;
+  double tj_prev = 0.0;
+#pragma unroll
+  for (int j = 0; j < kPB; j++) {
+    if (j > 0) {  // what is left of pivot j - 1 (its update of column j was done before column j went out)
+#pragma unroll
+      for (int c = j + 1; c < kPB; c++) a[c] -= tj_prev * U[j - 1][c];  // meaningful for lanes >= c
+    }
+    // the reciprocal (MUFU.RCP64H seed) is good for any normal double; only the square root, which is
+    // not computed here, needs the narrower range
+    const bool usable = d > 1e-300 && d < 1e300;  // false for d <= 0 and NaN
+    abn |= !usable;
+    const double rc = chain_rcp(usable ? d : 1.0);
+    const double tj = a[j] * rc;  // A[lane][j] / d
+    if (j + 1 < kPB) {
+      a[j + 1] -= tj * U[j][j + 1];
+      U[j + 1][lane] = a[j + 1];
+      M3R_WARP_FENCE();
+      *prog_u = j + 2;  // every lane stores the same value
+      d = U[j + 1][j + 1];
+    }
+    tj_prev = tj;
+  }
+  M3R_WARP_FENCE();
+  __syncwarp();
+  return abn;
+}
+
+// follower side of prog_u
+__device__ __forceinline__ void wait_columns(volatile int *prog_u, int need) {
+  while (*prog_u < need) __nanosleep(32);
+  __threadfence_block();
+}
+
+// warp_chol32_scale (a warp that is idle during the factorisation): column c of L is column c of U times
+// 1/sqrt(d_c).  Publishes L11[.][c] (zeros above the diagonal) and dinv[c] in groups of kFollowGroup
+// columns, then raises *prog: the TRSM rows, the y_k chain and the inverse of the block follow it.
+// The special cases live here, off the chain: d <= 0 (the chain has flagged the step as failed;
+// keep the factor finite) and pivots outside the range of the fp32-seeded square root.
+__device__ __forceinline__ void warp_chol32_scale(double (*U)[kPB], int lane, double *dinv,
+                                                  double (*L11)[kPB + 1], volatile int *prog_u,
+                                                  volatile int *prog);
+#ifdef M3R_TEST_VARIANTS  // the one-warp-does-everything loop: the cluster solver of the variants build still uses it
 // 32x32 lower Cholesky by one warp: lane r holds row r in registers (a[c], c <= r meaningful).
 // Returns the reciprocal pivots through dinv[] (shared) and sets *bad on a non-positive pivot.
 // Column j travels between the lanes through `col` (32 doubles of shared memory), one round trip
@@ -143,6 +212,8 @@ __device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *col
   *prog = kPB;
 }
 
+#endif
+
 // follower side: block until pivot c of this panel's POTRF is published
 // (Called once per group of pivots, with a back-off: every poll is a shared-memory load in the
 // pipe the POTRF chain's own stores and loads go through; polling every pivot from four warps cost
@@ -153,6 +224,40 @@ __device__ __forceinline__ void wait_pivot(volatile int *prog, int c) {
 }
 constexpr int kFollowGroup = 4;  // TRSM rows and y_k follow the POTRF in groups of this many pivots
 constexpr int kInvGroup = 8;     // the block inverse (off the critical path) in groups of this many
+
+__device__ __forceinline__ void warp_chol32_scale(double (*U)[kPB], int lane, double *dinv,
+                                                  double (*L11)[kPB + 1], volatile int *prog_u,
+                                                  volatile int *prog) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < kPB; c0 += kFollowGroup) {
+    wait_columns(prog_u, c0 + kFollowGroup);
+    double r[kFollowGroup];
+    bool plain = true;
+#pragma unroll
+    for (int i = 0; i < kFollowGroup; i++) {
+      r[i] = U[c0 + i][c0 + i];
+      plain = plain && r[i] > 1e-30 && r[i] < 1e30;
+    }
+    if (plain) {  // four independent chains, interleaved
+#pragma unroll
+      for (int i = 0; i < kFollowGroup; i++) r[i] = chain_rsqrt(r[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < kFollowGroup; i++) {
+        const double d = r[i];
+        r[i] = !(d > 0.0) ? 1.0 : (d > 1e-30 && d < 1e30) ? chain_rsqrt(d) : rsqrt_wide_range(d);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kFollowGroup; i++) {
+      const int c = c0 + i;
+      dinv[c] = r[i];  // every lane holds the same value
+      L11[lane][c] = (lane >= c) ? U[c][lane] * r[i] : 0.0;
+    }
+    __syncwarp();
+    *prog = c0 + kFollowGroup;
+  }
+}
 
 template <int TILE>  // 32 or 64: A22 tile (tr, tc) -= L21[tr] L21[tc]^T
 __device__ __forceinline__ void coop_update_tile(double *__restrict__ A, int D, int k0, int pb,
@@ -231,7 +336,8 @@ struct CoopSmem {
   double L11[kPB][kPB + 1];
   double Ad[kPB][kPB + 1];   // diagonal block with the previous panel's update folded in
   double Ls[kPB][kLs];       // previous panel's L21, rows of the diagonal block
-  double dinv[kPB], yk[kPB], bk[kPB], col[kPB];
+  double U[kPB][kPB];        // unscaled columns of the factor, U[c][row] (warp_chol32_chain)
+  double dinv[kPB], yk[kPB], bk[kPB];
   double dpart[64 * 16];     // second half of the diagonal-block update (k = 16..31)
   union {
     struct {
@@ -243,7 +349,8 @@ struct CoopSmem {
     } b;
   } u;
   int bad;
-  int prog;  // pivots of the current panel's POTRF that are published (warp_chol32)
+  int prog;    // scaled columns of L11 (and dinv) that are published (warp_chol32_scale)
+  int prog_u;  // complete columns of U (warp_chol32_chain)
 };
 constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
 
@@ -274,8 +381,10 @@ __global__ void __launch_bounds__(kCoopThreads)
   long long aprof_t = 0;
 #endif
   __syncthreads();
-  // warp roles in phase A: 0 = POTRF (alone on its scheduler: warp 4 idles), 1,2,3,6 = the
-  // CTA's 128 panel rows (look-ahead update, TRSM, rhs), 5 = forward-substitution chain y_k
+  // warp roles in phase A: 0 = elimination chain of the diagonal block (alone on its scheduler: warp 4
+  // idles), 7 = square roots and scaled columns behind it, 1, 2 = the CTA's 64 panel rows (look-ahead
+  // update, TRSM, rhs; 3 and 6 help with their loads), 3 = inverse of the block (CTA of the first
+  // rows only), 5 = forward-substitution chain y_k
   const bool trsm_warp = warp >= 1 && warp <= kTrsmWarps;  // warps 1, 2: schedulers 1, 2
   const int trsm_slot = warp - 1;
   const bool diag_warp = warp == 0 || warp == 4 || warp == 5 || warp == 7;
@@ -312,7 +421,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         S.Ls[r][c] = (la && r < pb) ? A[g + kp + c] : 0.0;
       }
       if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
-      if (t == 0) S.prog = 0;  // no pivot of this panel is published yet
+      if (t == 0) S.prog = 0, S.prog_u = 0;  // nothing of this panel is published yet
       __syncthreads();
       COOP_ATICK(8);
 #ifdef M3R_COOP_PROF
@@ -393,12 +502,14 @@ __global__ void __launch_bounds__(kCoopThreads)
       }
       COOP_ATICK(9);
       if (warp == 0) {
-        // 3. POTRF (rows in registers, shuffles)
+        // 3. POTRF, elimination chain (rows in registers); warp 7 scales the columns behind it
         double a[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++) a[c] = (c <= lane) ? S.Ad[lane][c] : 0.0;
-        warp_chol32(a, lane, S.col, dinv, &bad, L11, prog);  // publishes L11 / dinv pivot by pivot
+        if (warp_chol32_chain(a, lane, S.U, &S.prog_u) && lane == 0) bad = 1;  // step discarded
         COOP_ATICK(10);
+      } else if (warp == 7) {
+        warp_chol32_scale(S.U, lane, dinv, L11, &S.prog_u, prog);  // publishes L11 / dinv, four columns at a time
       } else if (trsm_warp) {
         // 4. this thread's row: fold in the previous panel's update while warp 0 factors
         const int r = trsm_slot * 32 + lane;
