@@ -1634,6 +1634,13 @@ extern "C" int m3r_debug_coop_profile(long long *out16) {
   M3R_CUDA_TRY(cudaMemcpyToSymbol(g_coop_prof, zero, sizeof(zero)));
   return M3R_OK;
 }
+extern "C" int m3r_debug_coop_stamps(long long *out16) {
+  long long zero[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  M3R_CUDA_TRY(cudaDeviceSynchronize());
+  M3R_CUDA_TRY(cudaMemcpyFromSymbol(out16, g_coop_stamp, sizeof(zero)));
+  M3R_CUDA_TRY(cudaMemcpyToSymbol(g_coop_stamp, zero, sizeof(zero)));
+  return M3R_OK;
+}
 #endif
 #ifdef M3R_TEST_VARIANTS
 extern "C" int m3r_debug_cluster_profile(long long *out9) {

@@ -55,7 +55,15 @@ __device__ long long g_coop_prof[16];  // [8..13]: phase A split of CTA 0, see C
       aprof_t = now_;                                     \
     }                                                     \
   } while (0)
+// when each role of CTA 0 reaches a point of the panel step, in cycles since the step began (summed
+// over the panels): read by m3r_debug_coop_stamps
+__device__ long long g_coop_stamp[16];
+#define COOP_STAMP(slot)                                                   \
+  do {                                                                     \
+    if (blockIdx.x == 0 && lane == 0) S.stamp[slot] = clock64() - S.t0;     \
+  } while (0)  /* to shared memory: a read-modify-write of a global counter stalls the warp 0.7 us */
 #else
+#define COOP_STAMP(slot) do { } while (0)
 #define COOP_TICK(slot) do { } while (0)
 #define COOP_TTICK(slot) do { } while (0)
 #define COOP_ATICK(slot) do { } while (0)
@@ -95,8 +103,24 @@ __device__ __forceinline__ double chain_rcp(double d) {
   return r;
 }
 
-// out-of-line so that the pivot chain's code stays small (never taken for sane systems)
-__device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
+// 1/sqrt(d) from the fp64 MUFU.RSQ64H seed (2^-22.9) and two Newton steps: no conversion to fp32 and
+// back on the way, and good for any normal double (the fp32-seeded chain_rsqrt needs 1e-30 < d < 1e30).
+__device__ __forceinline__ double chain_rsqrt64(double d) {
+  double r;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = fma(-d * r, r, 1.0);
+  r = fma(0.5 * r, e, r);
+  e = fma(-d * r, r, 1.0);
+  r = fma(0.5 * r, e, r);
+  return r;
+}
+
+// A pivot the factorisation can use: positive, finite, 2^-997 <= d < 2^996 (so that the MUFU seeds of
+// 1/d and 1/sqrt(d) and their Newton steps stay in range).  One integer compare on the high word
+// instead of two DSETP: false for zero, negatives, denormals, infinities and NaN.
+__device__ __forceinline__ bool pivot_usable(double d) {
+  return static_cast<unsigned>(__double2hiint(d)) - 0x01a00000u < 0x7c900000u;
+}
 
 // ---- factorisation of the 32x32 diagonal block: one warp runs the elimination chain, another scales
 //
@@ -116,6 +140,23 @@ __device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
 // instructions in order, so a store by lane a is visible to the load by lane b that follows it in
 // program order.  WARP_FENCE keeps the compiler from reordering them.
 // *prog_u = number of complete columns of U (U[c][c] is the pivot d_c).
+// back-off of the warps that poll a progress counter in shared memory (build parameters for tools/)
+#ifndef M3R_POLL_NS
+#define M3R_POLL_NS 100
+#endif
+#ifndef M3R_POLL_U_NS
+#define M3R_POLL_U_NS 32
+#endif
+#if M3R_POLL_NS > 0
+#define M3R_POLL_SLEEP() __nanosleep(M3R_POLL_NS)
+#else
+#define M3R_POLL_SLEEP() do { } while (0)
+#endif
+#if M3R_POLL_U_NS > 0
+#define M3R_POLL_U_SLEEP() __nanosleep(M3R_POLL_U_NS)
+#else
+#define M3R_POLL_U_SLEEP() do { } while (0)
+#endif
 #define M3R_WARP_FENCE() asm volatile("" ::: "memory")
 __device__ __forceinline__ bool warp_chol32_chain(double a[kPB], int lane, double (*U)[kPB],
                                                   volatile int *prog_u) {
@@ -134,7 +175,7 @@ __device__ __forceinline__ bool warp_chol32_chain(double a[kPB], int lane, doubl
     }
     // the reciprocal (MUFU.RCP64H seed) is good for any normal double; only the square root, which is
     // not computed here, needs the narrower range
-    const bool usable = d > 1e-300 && d < 1e300;  // false for d <= 0 and NaN
+    const bool usable = pivot_usable(d);  // false for d <= 0 and NaN
     abn |= !usable;
     const double rc = chain_rcp(usable ? d : 1.0);
     const double tj = a[j] * rc;  // A[lane][j] / d
@@ -154,19 +195,21 @@ __device__ __forceinline__ bool warp_chol32_chain(double a[kPB], int lane, doubl
 
 // follower side of prog_u
 __device__ __forceinline__ void wait_columns(volatile int *prog_u, int need) {
-  while (*prog_u < need) __nanosleep(32);
-  __threadfence_block();
+  while (*prog_u < need) M3R_POLL_U_SLEEP();
+  M3R_WARP_FENCE();  // see wait_pivot
 }
 
 // warp_chol32_scale (a warp that is idle during the factorisation): column c of L is column c of U times
 // 1/sqrt(d_c).  Publishes L11[.][c] (zeros above the diagonal) and dinv[c] in groups of kFollowGroup
 // columns, then raises *prog: the TRSM rows, the y_k chain and the inverse of the block follow it.
-// The special cases live here, off the chain: d <= 0 (the chain has flagged the step as failed;
-// keep the factor finite) and pivots outside the range of the fp32-seeded square root.
+// An unusable pivot (d <= 0, NaN, outside 2^-997 .. 2^996) was replaced by 1 in the chain, which has
+// flagged the step as failed; the factor is kept finite here the same way.
 __device__ __forceinline__ void warp_chol32_scale(double (*U)[kPB], int lane, double *dinv,
                                                   double (*L11)[kPB + 1], volatile int *prog_u,
                                                   volatile int *prog);
 #ifdef M3R_TEST_VARIANTS  // the one-warp-does-everything loop: the cluster solver of the variants build still uses it
+// out-of-line so that the pivot chain's code stays small (never taken for sane systems)
+__device__ __noinline__ double rsqrt_wide_range(double d) { return rsqrt(d); }
 // 32x32 lower Cholesky by one warp: lane r holds row r in registers (a[c], c <= r meaningful).
 // Returns the reciprocal pivots through dinv[] (shared) and sets *bad on a non-positive pivot.
 // Column j travels between the lanes through `col` (32 doubles of shared memory), one round trip
@@ -219,8 +262,13 @@ __device__ __forceinline__ void warp_chol32(double a[kPB], int lane, double *col
 // pipe the POTRF chain's own stores and loads go through; polling every pivot from four warps cost
 // the chain 15 %.)
 __device__ __forceinline__ void wait_pivot(volatile int *prog, int c) {
-  while (*prog <= c) __nanosleep(100);
-  __threadfence_block();
+  while (*prog <= c) M3R_POLL_SLEEP();
+  // No MEMBAR: the producer warp stores the columns and then the counter, this warp loads the counter
+  // and then the columns, and the SM's shared-memory pipe performs one warp's instructions in
+  // order, so the compiler is the only thing that could reorder them.  __threadfence_block() here is a
+  // MEMBAR.SC.CTA per group of pivots: measured, it keeps a follower 1050 cycles behind the
+  // factorisation instead of 530 (tools/ubench_potrf2.cu), twice in series (scaling warp, then TRSM).
+  M3R_WARP_FENCE();
 }
 constexpr int kFollowGroup = 4;  // TRSM rows and y_k follow the POTRF in groups of this many pivots
 constexpr int kInvGroup = 8;     // the block inverse (off the critical path) in groups of this many
@@ -231,28 +279,20 @@ __device__ __forceinline__ void warp_chol32_scale(double (*U)[kPB], int lane, do
 #pragma unroll 1
   for (int c0 = 0; c0 < kPB; c0 += kFollowGroup) {
     wait_columns(prog_u, c0 + kFollowGroup);
-    double r[kFollowGroup];
-    bool plain = true;
+    double r[kFollowGroup], u[kFollowGroup];
 #pragma unroll
     for (int i = 0; i < kFollowGroup; i++) {
-      r[i] = U[c0 + i][c0 + i];
-      plain = plain && r[i] > 1e-30 && r[i] < 1e30;
+      const double d = U[c0 + i][c0 + i];
+      u[i] = U[c0 + i][lane];
+      r[i] = pivot_usable(d) ? d : 1.0;  // an unusable pivot: the chain has flagged the step as failed
     }
-    if (plain) {  // four independent chains, interleaved
 #pragma unroll
-      for (int i = 0; i < kFollowGroup; i++) r[i] = chain_rsqrt(r[i]);
-    } else {
-#pragma unroll
-      for (int i = 0; i < kFollowGroup; i++) {
-        const double d = r[i];
-        r[i] = !(d > 0.0) ? 1.0 : (d > 1e-30 && d < 1e30) ? chain_rsqrt(d) : rsqrt_wide_range(d);
-      }
-    }
+    for (int i = 0; i < kFollowGroup; i++) r[i] = chain_rsqrt64(r[i]);  // four independent chains
 #pragma unroll
     for (int i = 0; i < kFollowGroup; i++) {
       const int c = c0 + i;
       dinv[c] = r[i];  // every lane holds the same value
-      L11[lane][c] = (lane >= c) ? U[c][lane] * r[i] : 0.0;
+      L11[lane][c] = (lane >= c) ? u[i] * r[i] : 0.0;
     }
     __syncwarp();
     *prog = c0 + kFollowGroup;
@@ -331,6 +371,32 @@ __device__ __forceinline__ void coop_invert_block(double (*L)[kPB + 1], const do
   Ld[kPB * kPB + lane] = dinv_blk[lane];
 }
 
+// half of the CTA's staged panel rows (L21 after the TRSM) to global memory, one row per instruction.
+// Full tiles (all but the last CTA's rows and the last panel) take a branch-free path: eight
+// shared-memory loads, then eight stores at 32-bit row offsets.  (A guarded load-store pair per row
+// compiles to a branch and a dependent chain of ten integer instructions: 70 cycles per row on an
+// in-order warp, 1.4 us per panel behind everything else.)
+__device__ __forceinline__ void coop_store_rows(double *__restrict__ A, int D, int k0, int pb, int row0,
+                                                int nrows, double (*Xr)[kPB + 1], int half, int lane) {
+  constexpr int kRowsPerWarp = kTrsmRows / 2;
+  const int n = nrows - half * kRowsPerWarp;  // rows of this half that exist
+  const double *src = &Xr[half * kRowsPerWarp][lane];
+  double *dst = A + static_cast<size_t>(row0 + half * kRowsPerWarp) * D + k0 + lane;
+  if (n >= kRowsPerWarp && pb == kPB) {
+#pragma unroll
+    for (int i = 0; i < kRowsPerWarp; i += 8) {
+      double v[8];
+#pragma unroll
+      for (int q = 0; q < 8; q++) v[q] = src[(i + q) * (kPB + 1)];
+#pragma unroll
+      for (int q = 0; q < 8; q++) dst[(i + q) * D] = v[q];  // the system has fewer than 2^31 entries
+    }
+  } else if (lane < pb) {
+#pragma unroll 1
+    for (int i = 0; i < n; i++) dst[i * D] = src[i * (kPB + 1)];
+  }
+}
+
 constexpr int kLs = kPB + 2;  // even leading dimension: 16-byte aligned pairs for LDS.128
 struct CoopSmem {
   double L11[kPB][kPB + 1];
@@ -351,6 +417,10 @@ struct CoopSmem {
   int bad;
   int prog;    // scaled columns of L11 (and dinv) that are published (warp_chol32_scale)
   int prog_u;  // complete columns of U (warp_chol32_chain)
+#ifdef M3R_COOP_PROF
+  long long t0;
+  long long stamp[16];
+#endif
 };
 constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
 
@@ -381,10 +451,11 @@ __global__ void __launch_bounds__(kCoopThreads)
   long long aprof_t = 0;
 #endif
   __syncthreads();
-  // warp roles in phase A: 0 = elimination chain of the diagonal block (alone on its scheduler: warp 4
-  // idles), 7 = square roots and scaled columns behind it, 1, 2 = the CTA's 64 panel rows (look-ahead
-  // update, TRSM, rhs; 3 and 6 help with their loads), 3 = inverse of the block (CTA of the first
-  // rows only), 5 = forward-substitution chain y_k
+  // warp roles in phase A (scheduler = warp % 4): 0 = elimination chain of the diagonal block, 4 = square
+  // roots and scaled columns behind it (same scheduler as the chain, whose instructions are sparse; on
+  // scheduler 3 it queued behind the DFMAs of the inverse and needed 700 cycles per group of four
+  // columns), 1, 2 = the CTA's 64 panel rows (look-ahead update, TRSM, rhs), 3 = inverse of the block
+  // (CTA of the first rows only), 5 = forward-substitution chain y_k, 6, 7 = store the rows of L21
   const bool trsm_warp = warp >= 1 && warp <= kTrsmWarps;  // warps 1, 2: schedulers 1, 2
   const int trsm_slot = warp - 1;
   const bool diag_warp = warp == 0 || warp == 4 || warp == 5 || warp == 7;
@@ -401,51 +472,64 @@ __global__ void __launch_bounds__(kCoopThreads)
     // ---------------- phase A (panel CTAs)
     for (int rc = blockIdx.x; rc < row_ctas; rc += gridDim.x) {
 #ifdef M3R_COOP_PROF
-      if (blockIdx.x == 0 && t == 0) aprof_t = clock64();
+      if (blockIdx.x == 0 && t == 0) aprof_t = clock64(), S.t0 = aprof_t;
+      __syncthreads();
 #endif
       const int row0 = k0 + pb + rc * kTrsmRows;
       const int nrows = max(0, min(kTrsmRows, D - row0));
       double (*L11)[kPB + 1] = S.L11;
       double *dinv = S.dinv;
       volatile int *prog = &S.prog;  // pivots of this panel's POTRF published so far
-      // 1. what the POTRF needs (diagonal block, the previous panel's rows of it, rhs) by all
-      //    threads; the CTA's 128 panel rows are loaded by the TRSM warps themselves AFTER this
-      //    barrier, beside the diagonal-block update and the POTRF instead of in front of them
+      // 1. everything phase A reads from L2, in ONE round trip by all threads: the diagonal block, the
+      //    previous panel's rows of it, the rhs, and the CTA's panel rows with their L21 of the
+      //    previous panel.  (Round 1 staged the rows after this barrier, beside the POTRF, which was
+      //    the critical path then; since the factorisation warp carries the chain only, the row path
+      //    -- loads, look-ahead fold, TRSM -- is, and a second round trip in front of it costs 1 us per panel.)
+      {
+        double vd[kPB * kPB / kCoopThreads], vs[kPB * kPB / kCoopThreads];
+        double vx[kTrsmRows * kPB / kCoopThreads], vl[kTrsmRows * kPB / kCoopThreads];
 #pragma unroll
-      for (int x = t; x < kPB * kPB; x += kCoopThreads) {
-        const int r = x / kPB, c = x % kPB;
-        const size_t g = static_cast<size_t>(k0 + r) * D;
-        double v = (r >= pb && r == c) ? 1.0 : 0.0;  // identity on the padding of the last panel
-        if (r < pb && c <= r) v = A[g + k0 + c];
-        S.Ad[r][c] = v;
-        S.Ls[r][c] = (la && r < pb) ? A[g + kp + c] : 0.0;
+        for (int i = 0; i < kPB * kPB / kCoopThreads; i++) {
+          const int x = t + i * kCoopThreads;
+          const int r = x / kPB, c = x % kPB;
+          const size_t g = static_cast<size_t>(k0 + r) * D;
+          vd[i] = (r >= pb && r == c) ? 1.0 : 0.0;  // identity on the padding of the last panel
+          if (r < pb && c <= r) vd[i] = A[g + k0 + c];
+          vs[i] = (la && r < pb) ? A[g + kp + c] : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < kTrsmRows * kPB / kCoopThreads; i++) {
+          const int x = t + i * kCoopThreads;
+          const int r = x / kPB, c = x % kPB;
+          const size_t g = static_cast<size_t>(row0 + r) * D;
+          vx[i] = (r < nrows && c < pb) ? A[g + k0 + c] : 0.0;
+          vl[i] = (la && r < nrows) ? A[g + kp + c] : 0.0;
+        }
+        if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
+        if (t == 0) S.prog = 0, S.prog_u = 0;  // nothing of this panel is published yet
+#pragma unroll
+        for (int i = 0; i < kPB * kPB / kCoopThreads; i++) {
+          const int x = t + i * kCoopThreads;
+          S.Ad[x / kPB][x % kPB] = vd[i];
+          S.Ls[x / kPB][x % kPB] = vs[i];
+        }
+#pragma unroll
+        for (int i = 0; i < kTrsmRows * kPB / kCoopThreads; i++) {
+          const int x = t + i * kCoopThreads;
+          S.u.a.Xr[x / kPB][x % kPB] = vx[i];
+          S.u.a.Lp[x / kPB][x % kPB] = vl[i];
+        }
       }
-      if (t < kPB) S.bk[t] = (t < pb) ? rhs[k0 + t] : 0.0;
-      if (t == 0) S.prog = 0, S.prog_u = 0;  // nothing of this panel is published yet
       __syncthreads();
       COOP_ATICK(8);
 #ifdef M3R_COOP_PROF
       if (blockIdx.x == 0 && t == 32) tprof_t = clock64();
 #endif
-      // the row loads are shared with the two warps that have nothing else to do (3 and 6): one
-      // batch of 32 independent loads per thread instead of eight dependent batches
-      const bool load_warp = trsm_warp || warp == 3 || warp == 6;
-      if (load_warp) {
-        const int tt = (trsm_warp ? trsm_slot : (warp == 3 ? 2 : 3)) * 32 + lane;
-#pragma unroll
-        for (int x = tt; x < kTrsmRows * kPB; x += 128) {
-          const int r = x / kPB, c = x % kPB;
-          const size_t g = static_cast<size_t>(row0 + r) * D;
-          S.u.a.Xr[r][c] = (r < nrows && c < pb) ? A[g + k0 + c] : 0.0;
-          S.u.a.Lp[r][c] = (la && r < nrows) ? A[g + kp + c] : 0.0;
-        }
-        if (trsm_warp) asm volatile("bar.sync 4, 128;");  // rows staged
-        else asm volatile("bar.arrive 4, 128;");
-      }
       if (warp == 3 && rc == 0) {
         // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot products
-        //    instead of a 32-pivot chain), on a warp that is idle once the rows are staged
+        //    instead of a 32-pivot chain), on a warp that has nothing else to do
         coop_invert_block(L11, dinv, ldiag + static_cast<size_t>(k0 / kPB) * kLdStride, lane, prog);
+        COOP_STAMP(8);
       }
       // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
       //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
@@ -502,14 +586,18 @@ __global__ void __launch_bounds__(kCoopThreads)
       }
       COOP_ATICK(9);
       if (warp == 0) {
-        // 3. POTRF, elimination chain (rows in registers); warp 7 scales the columns behind it
+        // 3. POTRF, elimination chain (rows in registers); warp 4 scales the columns behind it
         double a[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++) a[c] = (c <= lane) ? S.Ad[lane][c] : 0.0;
+        COOP_STAMP(0);
         if (warp_chol32_chain(a, lane, S.U, &S.prog_u) && lane == 0) bad = 1;  // step discarded
+        COOP_STAMP(1);
         COOP_ATICK(10);
-      } else if (warp == 7) {
+      } else if (warp == 4) {
+        COOP_STAMP(2);
         warp_chol32_scale(S.U, lane, dinv, L11, &S.prog_u, prog);  // publishes L11 / dinv, four columns at a time
+        COOP_STAMP(3);
       } else if (trsm_warp) {
         // 4. this thread's row: fold in the previous panel's update while warp 0 factors
         const int r = trsm_slot * 32 + lane;
@@ -530,6 +618,7 @@ __global__ void __launch_bounds__(kCoopThreads)
           }
         }
         COOP_TTICK(0);
+        if (warp == 1) COOP_STAMP(4);
         const double rhs_old = has_row ? rhs[row] : 0.0;  // in flight during the TRSM
         COOP_TTICK(1);
         // right-looking TRSM: independent updates per column -> ILP.  Column c of L11 is final
@@ -542,13 +631,15 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
           for (int k = c + 1; k < kPB; k++) x[k] -= xc * L11[k][c];
         }
-        if (has_row) {
-          double *Ar = A + static_cast<size_t>(row) * D + k0;
+        if (warp == 1) COOP_STAMP(5);
+        // the rows go back through shared memory: a thread storing its own row issues 32 STG that
+        // each touch 32 different lines (1 us of LSU time per panel, behind the factorisation);
+        // staged, the two spare warps store whole rows, one coalesced instruction per row
 #pragma unroll
-          for (int c = 0; c < kPB; c++)
-            if (c < pb) Ar[c] = x[c];
-        }
+        for (int c = 0; c < kPB; c++) S.u.a.Xr[r][c] = x[c];  // this thread's own slots
+        asm volatile("bar.arrive 5, 128;");  // warps 6 and 7 store them; this warp goes on to the rhs
         COOP_TTICK(2);
+        if (warp == 1) COOP_STAMP(6);
         asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));  // y_k ready
         if (has_row) {
           double d0 = 0.0, d1 = 0.0, d2 = 0.0, d3 = 0.0;
@@ -560,6 +651,12 @@ __global__ void __launch_bounds__(kCoopThreads)
           rhs[row] = rhs_old - ((d0 + d1) + (d2 + d3));
         }
         COOP_TTICK(3);
+        if (warp == 1) COOP_STAMP(12);
+      } else if (warp == 6 || warp == 7) {
+        asm volatile("bar.sync 5, 128;");  // the TRSM warps have staged their rows of L21
+        if (warp == 6) COOP_STAMP(10);
+        coop_store_rows(A, D, k0, pb, row0, nrows, S.u.a.Xr, warp == 6 ? 0 : 1, lane);
+        if (warp == 6) COOP_STAMP(11);
       } else if (warp == 5) {
         // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp and one pivot
         //    behind it: step c needs L11[.][c] and dinv[c] only
@@ -573,10 +670,16 @@ __global__ void __launch_bounds__(kCoopThreads)
         }
         __syncwarp();
         if (lane >= pb) yk[lane] = 0.0;
+        COOP_STAMP(7);
         asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));
         if (rc == 0 && lane < pb) xbuf[k0 + lane] = mine;
       }
       __syncthreads();
+      if (warp == 0) COOP_STAMP(9);
+#ifdef M3R_COOP_PROF
+      __syncthreads();
+      if (blockIdx.x == 0 && t < 16) g_coop_stamp[t] += S.stamp[t];
+#endif
       COOP_ATICK(13);
     }
     COOP_TICK(0);

@@ -50,9 +50,12 @@ def coop_profile():
     D = synth.GN_DEFAULTS
     g = bench.make_gn_graph(int(os.environ.get("KF", 64)), "cuda")
     out = (ctypes.c_longlong * 16)()
+    st = (ctypes.c_longlong * 16)()
     _lib.lib.m3r_debug_coop_profile(out)
+    _lib.lib.m3r_debug_coop_stamps(st)
     r = bench.time_gn(g, D, "rays", 0, 1, reps=1)
     _lib.lib.m3r_debug_coop_profile(out)
+    _lib.lib.m3r_debug_coop_stamps(st)
     n = max(out[6], 1)
     names = ["phaseA", "sync1", "phaseB", "sync2", "backward", "finish", "launches", "-", "A:loads", "A:diag update",
              "A:potrf", "T:row loads + fold", "T:wait for L11", "A:wait for the TRSM warps", "T:trsm + row stores",
@@ -61,6 +64,15 @@ def coop_profile():
     for k, nm in enumerate(names):
         if nm not in ("launches", "-"):
             print(f"  {nm:18s} {out[k] / n / 1.965e3:8.1f} us per launch")
+
+
+    panels = max(out[6], 1) * ((7 * (int(os.environ.get("KF", 64)) - 1) + 31) // 32)
+    stamps = ["chain starts", "chain done", "scaling warp starts", "scaling warp done", "TRSM warp: fold done",
+              "TRSM warp: TRSM done", "TRSM warp: rows staged", "y_k done", "inverse done", "CTA barrier passed",
+              "store warp: rows are staged", "store warp: rows stored", "TRSM warp: rhs updated"]
+    print("  timeline of one panel step in CTA 0 (us since the step began, mean over the panels):")
+    for k, nm in enumerate(stamps):
+        print(f"    {nm:26s} {st[k] / panels / 1.965e3:6.2f}")
 
 
 if __name__ == "__main__" and "coop" in sys.argv:

@@ -119,9 +119,12 @@ __device__ __forceinline__ bool chol_flat_nobar(double a[kPB], int lane, volatil
   *prog = kPB;
   return abn;
 }
+template <int FENCE>  // 0: compiler fence only, 1: __threadfence_block (MEMBAR.SC.CTA), 2: fence.acq_rel.cta
 __device__ __forceinline__ void wait_pivot(volatile int *prog, int c) {
   while (*prog <= c) __nanosleep(100);
-  __threadfence_block();
+  if (FENCE == 1) __threadfence_block();
+  else if (FENCE == 2) asm volatile("fence.acq_rel.cta;" ::: "memory");
+  else asm volatile("" ::: "memory");
 }
 
 struct Smem {
@@ -130,7 +133,7 @@ struct Smem {
   int bad, prog;
 };
 
-template <int FLAT, int MODE>  // FLAT 0 product loop, 1 branch-free, 2 branch- and barrier-free; MODE 0: 32 threads; 1: 256 threads, others idle; 2: pollers; 3: pollers working
+template <int FLAT, int MODE, int FENCE = 1>  // FLAT 0 product loop, 1 branch-free, 2 branch- and barrier-free; MODE 0: 32 threads; 1: 256 threads, others idle; 2: pollers; 3: pollers working
 __global__ void __launch_bounds__(256, 1) k(const double *A, double *out, long long *cyc, int reps) {
   __shared__ Smem S;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(256, 1) k(const double *A, double *out, long l
         chol_branchy(a, lane, S.col, S.dinv, &S.bad, S.L11, &S.prog);
       }
       const long long t1 = clock64();
-      if (lane == 0) cyc[rep] = t1 - t0;
+      if (lane == 0) cyc[rep] = t1 - t0, cyc[8] = t1;
 #pragma unroll
       for (int c = 0; c < kPB; c++) out[lane * kPB + c] = (c <= lane) ? a[c] : 0.0;
     } else if (MODE >= 2 && (warp == 1 || warp == 2 || warp == 3 || warp == 5)) {
@@ -159,7 +162,7 @@ __global__ void __launch_bounds__(256, 1) k(const double *A, double *out, long l
       for (int c = 0; c < kPB; c++) x[c] = A[lane * kPB + c] + warp;
 #pragma unroll
       for (int c = 0; c < kPB; c++) {
-        if ((c % 4) == 0) wait_pivot(&S.prog, c + 3);
+        if ((c % 4) == 0) wait_pivot<FENCE>(&S.prog, c + 3);
         if (MODE == 3) {
           const double xc = x[c] * S.dinv[c];
           x[c] = xc;
@@ -167,6 +170,7 @@ __global__ void __launch_bounds__(256, 1) k(const double *A, double *out, long l
           for (int q = c + 1; q < kPB; q++) x[q] -= xc * S.L11[q][c];
         }
       }
+      if (lane == 0) cyc[8 + warp] = clock64();
       if (MODE == 3) {
         double s = 0;
 #pragma unroll
@@ -195,7 +199,7 @@ int main() {
   long long *dc;
   cudaMalloc(&dA, sizeof(h));
   cudaMalloc(&dO, sizeof(h) + 4096);
-  cudaMalloc(&dc, 64);
+  cudaMalloc(&dc, 256);
   cudaMemcpy(dA, h, sizeof(h), cudaMemcpyHostToDevice);
   run<0, 0>("P0 product loop, one warp", dA, dO, dc);
   run<0, 1>("P1 product loop, warp 0 of 256 threads", dA, dO, dc);
@@ -209,6 +213,18 @@ int main() {
   run<2, 1>("R1 warp 0 of 256 threads", dA, dO, dc);
   run<2, 2>("R2 + 4 warps polling", dA, dO, dc);
   run<2, 3>("R3 + pollers working", dA, dO, dc);
+  {
+    long long hc[16];
+    k<2, 3, 1><<<1, 256>>>(dA, dO, dc, 6);
+    cudaMemcpy(hc, dc, 128, cudaMemcpyDeviceToHost);
+    printf("followers behind the factorisation, MEMBAR.SC.CTA per group: %lld %lld %lld %lld cycles (potrf %lld)\n", hc[9] - hc[8], hc[10] - hc[8], hc[11] - hc[8], hc[13] - hc[8], hc[5]);
+    k<2, 3, 2><<<1, 256>>>(dA, dO, dc, 6);
+    cudaMemcpy(hc, dc, 128, cudaMemcpyDeviceToHost);
+    printf("followers behind the factorisation, fence.acq_rel.cta:      %lld %lld %lld %lld cycles (potrf %lld)\n", hc[9] - hc[8], hc[10] - hc[8], hc[11] - hc[8], hc[13] - hc[8], hc[5]);
+    k<2, 3, 0><<<1, 256>>>(dA, dO, dc, 6);
+    cudaMemcpy(hc, dc, 128, cudaMemcpyDeviceToHost);
+    printf("followers behind the factorisation, compiler fence only:    %lld %lld %lld %lld cycles (potrf %lld)\n", hc[9] - hc[8], hc[10] - hc[8], hc[11] - hc[8], hc[13] - hc[8], hc[5]);
+  }
   double o[kPB * kPB], ref[kPB * kPB];
   k<0, 1><<<1, 256>>>(dA, dO, dc, 1);
   cudaMemcpy(ref, dO, sizeof(ref), cudaMemcpyDeviceToHost);
