@@ -458,7 +458,9 @@ __global__ void __launch_bounds__(kCoopThreads)
   // (CTA of the first rows only), 5 = forward-substitution chain y_k, 6, 7 = store the rows of L21
   const bool trsm_warp = warp >= 1 && warp <= kTrsmWarps;  // warps 1, 2: schedulers 1, 2
   const int trsm_slot = warp - 1;
-  const bool diag_warp = warp == 0 || warp == 4 || warp == 5 || warp == 7;
+  // diagonal-block update on schedulers 0 and 3 only: 1 and 2 belong to the look-ahead fold of the TRSM
+  // warps (1024 DFMA per row) at that moment; with warp 5 in this group the update took 1.5 us and the fold 2.6
+  const bool diag_warp = (warp & 3) == 0 || (warp & 3) == 3;  // warps 0, 4, 3, 7
 
   for (int k0 = 0; k0 < D; k0 += kPB) {
     const int pb = min(kPB, D - k0);
@@ -525,12 +527,6 @@ __global__ void __launch_bounds__(kCoopThreads)
 #ifdef M3R_COOP_PROF
       if (blockIdx.x == 0 && t == 32) tprof_t = clock64();
 #endif
-      if (warp == 3 && rc == 0) {
-        // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot products
-        //    instead of a 32-pivot chain), on a warp that has nothing else to do
-        coop_invert_block(L11, dinv, ldiag + static_cast<size_t>(k0 / kPB) * kLdStride, lane, prog);
-        COOP_STAMP(8);
-      }
       // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
       //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
       //    272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner
@@ -541,7 +537,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         // two accumulators per output (even and odd columns of Ls): the dependent DFMA chain is
         // what this step costs (fp64 latency, not issue), and it halves
         double acc[4][4], acc1[4][4];
-        const int u = ((warp == 0) ? 0 : (warp == 4) ? 1 : (warp == 5) ? 2 : 3) * 32 + lane;
+        const int u = ((warp == 0) ? 0 : (warp == 4) ? 1 : (warp == 3) ? 2 : 3) * 32 + lane;
         const int tile = u & 63, half = u >> 6;
         const int tr = tile >> 3, tc = tile & 7;
 #pragma unroll
@@ -574,7 +570,7 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
             for (int k = 0; k < 4; k++) S.dpart[(i * 4 + k) * 64 + tile] = acc[i][k];
         }
-        asm volatile("bar.sync 3, 128;");  // warps 0, 4, 5, 7
+        asm volatile("bar.sync 3, 128;");  // warps 0, 4, 3, 7
         if (half == 0) {
 #pragma unroll
           for (int i = 0; i < 4; i++)
@@ -583,6 +579,9 @@ __global__ void __launch_bounds__(kCoopThreads)
               S.Ad[tr + 8 * i][tc + 8 * k] -= acc[i][k] + S.dpart[(i * 4 + k) * 64 + tile];
         }
         asm volatile("bar.sync 3, 128;");  // the updated diagonal block is complete
+#ifdef M3R_FOLD_AFTER_DIAG
+        asm volatile("bar.arrive 6, 192;");
+#endif
       }
       COOP_ATICK(9);
       if (warp == 0) {
@@ -606,6 +605,9 @@ __global__ void __launch_bounds__(kCoopThreads)
         double x[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++) x[c] = S.u.a.Xr[r][c];
+#ifdef M3R_FOLD_AFTER_DIAG
+        if (la) asm volatile("bar.sync 6, 192;");  // experiment: the fold starts when the diagonal update is done
+#endif
         if (la) {
 #pragma unroll 2
           for (int j = 0; j < kPB; j += 2) {
@@ -652,6 +654,13 @@ __global__ void __launch_bounds__(kCoopThreads)
         }
         COOP_TTICK(3);
         if (warp == 1) COOP_STAMP(12);
+      } else if (warp == 3) {
+        // 6. M = L11^-1 for the backward phase (x_k = M^T y_k is then 32 independent dot products
+        //    instead of a 32-pivot chain), on a warp that has nothing else to do
+        if (rc == 0) {
+          coop_invert_block(L11, dinv, ldiag + static_cast<size_t>(k0 / kPB) * kLdStride, lane, prog);
+          COOP_STAMP(8);
+        }
       } else if (warp == 6 || warp == 7) {
         asm volatile("bar.sync 5, 128;");  // the TRSM warps have staged their rows of L21
         if (warp == 6) COOP_STAMP(10);
@@ -736,10 +745,14 @@ __global__ void __launch_bounds__(kCoopThreads)
     __syncthreads();
     int buf = 0;
     constexpr int kUpd = kCoopThreads - 32;  // update threads (warps 1..7)
+    // Update thread j0 loads the step's 32 rows of L at BOTH of its first two columns (j0 and j0 + 224:
+    // D <= 480 needs no third) before the barrier, beside warp 0's multiply: one L2 round trip per step
+    // where k0 > 224 used to take two.  (Keeping the first column one step ahead in registers as well
+    // was tried: 0.1575 ms at D = 441 but spills, and slower at D = 105 and D = 1785.)
+    const int j0 = t - 32, j1 = j0 + kUpd;
     for (int k0 = last; k0 >= 0; k0 -= kPB, buf ^= 1) {
       const int pb = min(kPB, D - k0);
-      double lv[kPB];
-      const int j0 = t - 32;
+      double lvA[kPB], lvB[kPB];
       if (warp == 0) {  // x_k = M^T y_k, M = L11^-1 (row-major in the buffer): one dot product per lane
         const double *Md = ldb + buf * kLdBuf;
         double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -760,7 +773,12 @@ __global__ void __launch_bounds__(kCoopThreads)
         if (j0 < k0) {
 #pragma unroll
           for (int c = 0; c < kPB; c++)
-            lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j0] : 0.0;
+            lvA[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j0] : 0.0;
+        }
+        if (j1 < k0) {
+#pragma unroll
+          for (int c = 0; c < kPB; c++)
+            lvB[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j1] : 0.0;
         }
         if (k0 > 0) {
           const double *src = ldiag + static_cast<size_t>(k0 / kPB - 1) * kLdStride;
@@ -776,15 +794,25 @@ __global__ void __launch_bounds__(kCoopThreads)
       __syncthreads();
       // y_j -= sum_c L[k0+c][j] x_k[c] for all j < k0: independent, coalesced rows of L
       if (warp != 0) {
-        for (int j = j0; j < k0; j += kUpd) {
-          if (j != j0) {
+        if (j0 < k0) {
+          double sacc = xs[j0];
 #pragma unroll
-            for (int c = 0; c < kPB; c++)
-              lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j] : 0.0;
-          }
+          for (int c = 0; c < kPB; c++) sacc -= lvA[c] * yk[c];
+          xs[j0] = sacc;
+        }
+        if (j1 < k0) {
+          double sacc = xs[j1];
+#pragma unroll
+          for (int c = 0; c < kPB; c++) sacc -= lvB[c] * yk[c];
+          xs[j1] = sacc;
+        }
+        for (int j = j1 + kUpd; j < k0; j += kUpd) {
+#pragma unroll
+          for (int c = 0; c < kPB; c++)
+            lvB[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j] : 0.0;
           double sacc = xs[j];
 #pragma unroll
-          for (int c = 0; c < kPB; c++) sacc -= lv[c] * yk[c];
+          for (int c = 0; c < kPB; c++) sacc -= lvB[c] * yk[c];
           xs[j] = sacc;
         }
       }
