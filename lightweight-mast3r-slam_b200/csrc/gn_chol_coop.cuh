@@ -299,52 +299,97 @@ __device__ __forceinline__ void warp_chol32_scale(double (*U)[kPB], int lane, do
   }
 }
 
-template <int TILE>  // 32 or 64: A22 tile (tr, tc) -= L21[tr] L21[tc]^T
-__device__ __forceinline__ void coop_update_tile(double *__restrict__ A, int D, int k0, int pb,
-                                                 int base, int tr, int tc, double (*Ra)[kPB + 1],
-                                                 double (*Rb)[kPB + 1], int t) {
-  constexpr int R = TILE / 16;  // outputs per thread per dimension
-  const int ty = t / 16, tx = t % 16;
-  double acc[R][R];
-#pragma unroll
-  for (int i = 0; i < R; i++)
-#pragma unroll
-    for (int j = 0; j < R; j++) {
-      const int gr = base + tr * TILE + ty + 16 * i, gc = base + tc * TILE + tx + 16 * j;
-      acc[i][j] = (gr < D && gc <= gr) ? A[static_cast<size_t>(gr) * D + gc] : 0.0;
-    }
-  __syncthreads();
-  for (int x = t; x < TILE * kPB; x += kCoopThreads) {
-    const int r = x / kPB, c = x % kPB;
-    const int ga = base + tr * TILE + r, gb = base + tc * TILE + r;
-    Ra[r][c] = (ga < D && c < pb) ? A[static_cast<size_t>(ga) * D + k0 + c] : 0.0;
-    Rb[r][c] = (gb < D && c < pb) ? A[static_cast<size_t>(gb) * D + k0 + c] : 0.0;
-  }
-  __syncthreads();
-#pragma unroll 8
-  for (int k = 0; k < kPB; k++) {
-    double av[R], bv[R];
-#pragma unroll
-    for (int i = 0; i < R; i++) av[i] = Ra[ty + 16 * i][k], bv[i] = Rb[tx + 16 * i][k];
-#pragma unroll
-    for (int i = 0; i < R; i++)
-#pragma unroll
-      for (int j = 0; j < R; j++) acc[i][j] -= av[i] * bv[j];
-  }
-#pragma unroll
-  for (int i = 0; i < R; i++)
-#pragma unroll
-    for (int j = 0; j < R; j++) {
-      const int gr = base + tr * TILE + ty + 16 * i, gc = base + tc * TILE + tx + 16 * j;
-      if (gr < D && gc <= gr) A[static_cast<size_t>(gr) * D + gc] = acc[i][j];
-    }
-}
-
 __device__ __forceinline__ void tile_from_index(int tile, int &tr, int &tc) {
   tr = static_cast<int>((sqrt(8.0 * tile + 1.0) - 1.0) * 0.5);
   while ((tr + 1) * (tr + 2) / 2 <= tile) tr++;
   while (tr * (tr + 1) / 2 > tile) tr--;
   tc = tile - tr * (tr + 1) / 2;
+}
+
+// Trailing update A22 -= L21 L21^T of one panel, the CTA's share of the lower TILE x TILE tiles (TILE = 32
+// or 64; tiles first, first + stride, ...), software-pipelined: while tile i is multiplied out of shared
+// memory, the operand panels L21[tr], L21[tc] and the accumulators of tile i + 1 are already in flight
+// (registers), and the operand panels alternate between two shared-memory buffers so that one CTA
+// barrier per tile is enough.  The first version took each tile on its own: accumulators from L2, barrier,
+// operands from L2, barrier, 1.7 us of DFMA, store -- two serialised round trips per tile, and at
+// D = 1785 CTA 0 waited 250 us per solve for this phase (profiles/r2_i_potrf_chain.md).
+template <int TILE>
+struct TileRegs {
+  static constexpr int R = TILE / 16;                      // outputs per thread per dimension
+  static constexpr int NL = TILE * kPB / kCoopThreads;     // operand elements per thread and panel
+  double ra[NL], rb[NL], acc[R][R];
+  int tr, tc;
+};
+
+template <int TILE>
+__device__ __forceinline__ void tile_issue_loads(const double *__restrict__ A, int D, int kp, int base,
+                                                 int tile, int t, TileRegs<TILE> &q) {
+  constexpr int R = TileRegs<TILE>::R, NL = TileRegs<TILE>::NL;
+  tile_from_index(tile, q.tr, q.tc);
+  const int ty = t / 16, tx = t % 16;
+#pragma unroll
+  for (int i = 0; i < NL; i++) {
+    const int x = t + i * kCoopThreads;
+    const int r = x / kPB, c = x % kPB;
+    const int ga = base + q.tr * TILE + r, gb = base + q.tc * TILE + r;
+    q.ra[i] = (ga < D) ? A[static_cast<size_t>(ga) * D + kp + c] : 0.0;
+    q.rb[i] = (gb < D) ? A[static_cast<size_t>(gb) * D + kp + c] : 0.0;
+  }
+#pragma unroll
+  for (int i = 0; i < R; i++)
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+      const int gr = base + q.tr * TILE + ty + 16 * i, gc = base + q.tc * TILE + tx + 16 * j;
+      q.acc[i][j] = (gr < D && gc <= gr) ? A[static_cast<size_t>(gr) * D + gc] : 0.0;
+    }
+}
+
+template <int TILE>
+__device__ __forceinline__ void coop_update_tiles(double *__restrict__ A, int D, int kp, int base, int ntiles,
+                                                  int first, int stride, double (*Ra)[64][kPB + 1],
+                                                  double (*Rb)[64][kPB + 1], int t) {
+  constexpr int R = TileRegs<TILE>::R, NL = TileRegs<TILE>::NL;
+  if (first >= ntiles) return;  // uniform over the CTA
+  const int ty = t / 16, tx = t % 16;
+  TileRegs<TILE> cur;
+  tile_issue_loads<TILE>(A, D, kp, base, first, t, cur);
+  int b = 0;
+  for (int tile = first;; tile += stride, b ^= 1) {
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+      const int x = t + i * kCoopThreads;
+      Ra[b][x / kPB][x % kPB] = cur.ra[i];
+      Rb[b][x / kPB][x % kPB] = cur.rb[i];
+    }
+    __syncthreads();  // buffer b is staged; every thread is done with buffer b ^ 1 (the tile before)
+    const bool more = tile + stride < ntiles;
+    TileRegs<TILE> nxt;
+    if (more) tile_issue_loads<TILE>(A, D, kp, base, tile + stride, t, nxt);
+    double acc[R][R];
+#pragma unroll
+    for (int i = 0; i < R; i++)
+#pragma unroll
+      for (int j = 0; j < R; j++) acc[i][j] = cur.acc[i][j];
+#pragma unroll 8
+    for (int k = 0; k < kPB; k++) {
+      double av[R], bv[R];
+#pragma unroll
+      for (int i = 0; i < R; i++) av[i] = Ra[b][ty + 16 * i][k], bv[i] = Rb[b][tx + 16 * i][k];
+#pragma unroll
+      for (int i = 0; i < R; i++)
+#pragma unroll
+        for (int j = 0; j < R; j++) acc[i][j] -= av[i] * bv[j];
+    }
+#pragma unroll
+    for (int i = 0; i < R; i++)
+#pragma unroll
+      for (int j = 0; j < R; j++) {
+        const int gr = base + cur.tr * TILE + ty + 16 * i, gc = base + cur.tc * TILE + tx + 16 * j;
+        if (gr < D && gc <= gr) A[static_cast<size_t>(gr) * D + gc] = acc[i][j];
+      }
+    if (!more) break;
+    cur = nxt;
+  }
 }
 
 // M = L^-1 of one factored 32x32 diagonal block (by one warp, lane = column of M), stored row-major
@@ -411,7 +456,7 @@ struct CoopSmem {
       double Lp[kTrsmRows][kLs];      // their L21 of the previous panel
     } a;
     struct {
-      double Ra[64][kPB + 1], Rb[64][kPB + 1];  // phase B tiles
+      double Ra[2][64][kPB + 1], Rb[2][64][kPB + 1];  // phase B operand panels, double-buffered
     } b;
   } u;
   int bad;
@@ -433,8 +478,8 @@ __global__ void __launch_bounds__(kCoopThreads)
   if (flags[0]) return;  // uniform over the grid (the flag only changes after the last barrier)
   extern __shared__ __align__(16) unsigned char coop_smem_raw[];
   CoopSmem &S = *reinterpret_cast<CoopSmem *>(coop_smem_raw);
-  double (*Ra)[kPB + 1] = S.u.b.Ra;
-  double (*Rb)[kPB + 1] = S.u.b.Rb;
+  double (*Ra)[64][kPB + 1] = S.u.b.Ra;
+  double (*Rb)[64][kPB + 1] = S.u.b.Rb;
   double *yk = S.yk;
   int &bad = S.bad;
   const int t = threadIdx.x;
@@ -703,20 +748,10 @@ __global__ void __launch_bounds__(kCoopThreads)
       if (u >= 0) {
         const int T64 = (m + 63) / 64;
         if (T64 * (T64 + 1) / 2 >= 2 * nu) {
-          const int ntiles = T64 * (T64 + 1) / 2;
-          for (int tile = u; tile < ntiles; tile += nu) {
-            int tr, tc;
-            tile_from_index(tile, tr, tc);
-            coop_update_tile<64>(A, D, kp, kPB, base, tr, tc, Ra, Rb, t);
-          }
+          coop_update_tiles<64>(A, D, kp, base, T64 * (T64 + 1) / 2, u, nu, Ra, Rb, t);
         } else {  // few tiles: 32x32 tiles spread the update over more SMs
           const int T32 = (m + 31) / 32;
-          const int ntiles = T32 * (T32 + 1) / 2;
-          for (int tile = u; tile < ntiles; tile += nu) {
-            int tr, tc;
-            tile_from_index(tile, tr, tc);
-            coop_update_tile<32>(A, D, kp, kPB, base, tr, tc, Ra, Rb, t);
-          }
+          coop_update_tiles<32>(A, D, kp, base, T32 * (T32 + 1) / 2, u, nu, Ra, Rb, t);
         }
       }
     }
