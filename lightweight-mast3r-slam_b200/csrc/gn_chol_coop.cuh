@@ -345,7 +345,7 @@ __device__ __forceinline__ void tile_issue_loads(const double *__restrict__ A, i
 }
 
 template <int TILE>
-__device__ __forceinline__ void coop_update_tiles(double *__restrict__ A, int D, int kp, int base, int ntiles,
+__device__ __noinline__ void coop_update_tiles(double *__restrict__ A, int D, int kp, int base, int ntiles,
                                                   int first, int stride, double (*Ra)[64][kPB + 1],
                                                   double (*Rb)[64][kPB + 1], int t) {
   constexpr int R = TileRegs<TILE>::R, NL = TileRegs<TILE>::NL;
@@ -442,6 +442,8 @@ __device__ __forceinline__ void coop_store_rows(double *__restrict__ A, int D, i
   }
 }
 
+constexpr int kBackMultiMin = 512;  // systems above this size run the backward substitution on all CTAs
+
 constexpr int kLs = kPB + 2;  // even leading dimension: 16-byte aligned pairs for LDS.128
 struct CoopSmem {
   double L11[kPB][kPB + 1];
@@ -468,6 +470,109 @@ struct CoopSmem {
 #endif
 };
 constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
+
+// Backward substitution L^T x = y for large systems, all CTAs (see the call site).  Out of line: it runs
+// once per solve and must not take part in the register allocation of the panel loop.
+__device__ __noinline__ void coop_backward_multi(cg::grid_group &grid, CoopSmem &S, double *__restrict__ A,
+                                                 const double *__restrict__ ldiag, int D,
+                                                 double *__restrict__ xbuf) {
+  const int t = threadIdx.x;
+  const int lane = t & 31, warp = t >> 5;
+  double *yk = S.yk;
+  constexpr int kSuper = 8 * kPB;
+  constexpr int kLdBufM = kPB * kPB + kPB;
+  double *xs = &S.u.a.Lp[0][0];   // the super-block's part of the vector (CTA 0)
+  double *ldb = &S.u.a.Xr[0][0];  // 2 x kLdBufM doubles: M = L11^-1 of the current / next panel (CTA 0)
+  double *red = &S.u.a.Xr[0][0];  // 8 x 32 partial sums (the other CTAs, and CTA 0 in the fold stage)
+  const int nsuper = (D + kSuper - 1) / kSuper;
+  for (int sp = nsuper - 1; sp >= 0; sp--) {
+    const int c0 = sp * kSuper, c1 = min(D, c0 + kSuper);
+    if (blockIdx.x == 0) {
+      const int lastp = ((c1 - 1) / kPB) * kPB;
+      for (int i = t; i < c1 - c0; i += kCoopThreads) xs[i] = __ldcg(&xbuf[c0 + i]);
+      for (int x = t; x < kLdBufM; x += kCoopThreads)
+        ldb[x] = ldiag[static_cast<size_t>(lastp / kPB) * kLdStride + x];
+      __syncthreads();
+      int buf = 0;
+      const int jl = t - 32;  // update thread -> column c0 + jl of the super-block (224 >= 256 - 32 columns)
+      for (int k0 = lastp; k0 >= c0; k0 -= kPB, buf ^= 1) {
+        const int pb = min(kPB, D - k0);
+        double lv[kPB];
+        if (warp == 0) {  // x_k = M^T y_k
+          const double *Md = ldb + buf * kLdBufM;
+          const double *ys = xs + (k0 - c0);
+          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+          for (int r = 0; r < kPB; r += 4) {
+            s0 += Md[(r + 0) * kPB + lane] * ((r + 0 < pb) ? ys[r + 0] : 0.0);
+            s1 += Md[(r + 1) * kPB + lane] * ((r + 1 < pb) ? ys[r + 1] : 0.0);
+            s2 += Md[(r + 2) * kPB + lane] * ((r + 2 < pb) ? ys[r + 2] : 0.0);
+            s3 += Md[(r + 3) * kPB + lane] * ((r + 3 < pb) ? ys[r + 3] : 0.0);
+          }
+          const double mine = (s0 + s1) + (s2 + s3);
+          __syncwarp();
+          yk[lane] = (lane < pb) ? mine : 0.0;
+          if (lane < pb) xs[k0 - c0 + lane] = mine;
+        } else {
+          if (c0 + jl < k0) {
+#pragma unroll
+            for (int c = 0; c < kPB; c++)
+              lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + c0 + jl] : 0.0;
+          }
+          if (k0 > c0) {  // M of the next panel of this super-block
+            const double *src = ldiag + static_cast<size_t>(k0 / kPB - 1) * kLdStride;
+            for (int x = jl; x < kLdBufM; x += kCoopThreads - 32) ldb[(buf ^ 1) * kLdBufM + x] = src[x];
+          }
+        }
+        __syncthreads();
+        if (warp != 0 && c0 + jl < k0) {
+          double sacc = xs[jl];
+#pragma unroll
+          for (int c = 0; c < kPB; c++) sacc -= lv[c] * yk[c];
+          xs[jl] = sacc;
+        }
+        __syncthreads();
+      }
+      for (int i = t; i < c1 - c0; i += kCoopThreads) xbuf[c0 + i] = xs[i];
+    }
+    if (c0 == 0) break;  // (uniform) nothing in front of the first super-block
+    __threadfence();
+    grid.sync();  // x of the super-block is in xbuf
+    // fold: y_j -= sum_{r in [c0, c1)} L[r][j] x_r for j < c0; a CTA takes 32 columns per pass, warp w
+    // the rows c0 + 32 w ..., lane = column: every load instruction is one 256-byte row segment
+    for (int jc = blockIdx.x * 32; jc < c0; jc += gridDim.x * 32) {
+      const int j = jc + lane;
+      const int r0 = c0 + warp * kPB;
+      double xv[kPB], part = 0.0;
+#pragma unroll
+      for (int c = 0; c < kPB; c++) xv[c] = (r0 + c < c1) ? __ldcg(&xbuf[r0 + c]) : 0.0;
+      if (j < c0) {
+        double lvf[kPB];
+#pragma unroll
+        for (int c = 0; c < kPB; c++)
+          lvf[c] = (r0 + c < c1) ? A[static_cast<size_t>(r0 + c) * D + j] : 0.0;
+        double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+#pragma unroll
+        for (int c = 0; c < kPB; c += 4) {
+          p0 = fma(lvf[c], xv[c], p0), p1 = fma(lvf[c + 1], xv[c + 1], p1);
+          p2 = fma(lvf[c + 2], xv[c + 2], p2), p3 = fma(lvf[c + 3], xv[c + 3], p3);
+        }
+        part = (p0 + p1) + (p2 + p3);
+      }
+      __syncthreads();  // red is free (previous pass, or CTA 0's use of the buffer as ldb)
+      red[warp * 32 + lane] = part;
+      __syncthreads();
+      if (warp == 0 && j < c0) {
+        double sum = 0.0;
+#pragma unroll
+        for (int w = 0; w < kCoopThreads / 32; w++) sum += red[w * 32 + lane];
+        xbuf[j] = __ldcg(&xbuf[j]) - sum;
+      }
+    }
+    __threadfence();
+    grid.sync();  // y in front of the super-block is up to date
+  }
+}
 
 __global__ void __launch_bounds__(kCoopThreads)
     gn_chol_solve_coop_kernel(double *__restrict__ sys, double *__restrict__ ldiag, int D,
@@ -759,9 +864,33 @@ __global__ void __launch_bounds__(kCoopThreads)
     grid.sync();
     COOP_TICK(1);
   }
+  // ---------------- backward substitution L^T x = y, x overwrites xbuf
+  // Large systems (D > kBackMultiMin), all CTAs: one CTA streaming the whole of L (12.7 MB at D = 1785)
+  // through its SM's L2 port took 213 us of a 0.78 ms solve, a quarter of it.  The columns are taken in
+  // super-blocks of 8 panels: CTA 0 solves inside the super-block (the triangle it reads is 256 columns
+  // wide at most: one load per thread and step), then every CTA folds the super-block's x into a slice
+  // of the columns in front of it (32 columns x 256 rows per CTA and pass, summed over the 8 warps),
+  // with a grid barrier on either side.  y and x live in xbuf (global) between the stages.
+  if (D > kBackMultiMin) {
+    coop_backward_multi(grid, S, A, ldiag, D, xbuf);
+    if (blockIdx.x != 0) return;
+    __syncthreads();
+    const bool failm = bad != 0;
+    COOP_TICK(4);
+    finish_step<kCoopThreads>(t, failm, D, xbuf, Twc, dx, num_poses, delta_thresh, flags);
+    COOP_TICK(5);
+#ifdef M3R_COOP_PROF
+    if (t == 0) {
+      for (int k = 0; k < 6; k++) g_coop_prof[k] += prof_acc[k];
+      for (int k = 0; k < 6; k++) g_coop_prof[8 + k] += aprof[k];
+      g_coop_prof[6] += 1;
+    }
+#endif
+    return;
+  }
   if (blockIdx.x != 0) return;
 
-  // ---------------- backward substitution L^T x = y (CTA 0), x overwrites xbuf
+  // ---------------- small and medium systems: CTA 0 alone
   // The vector lives in shared memory for the whole phase, the diagonal block of the NEXT step
   // is prefetched by the idle warps while warp 0 walks the current 32-pivot chain, and the
   // update threads issue their loads of L before the barrier that publishes x_k: per block the
@@ -769,8 +898,8 @@ __global__ void __launch_bounds__(kCoopThreads)
   __syncthreads();
   const bool fail = bad != 0;
   constexpr int kLdBuf = kPB * kPB + kPB;
-  constexpr int kXsCap = kTrsmRows * kLs;  // doubles available in S.u.a.Lp
-  if (!fail && D <= kXsCap) {
+  static_assert(kBackMultiMin <= kTrsmRows * kLs, "the vector has to fit S.u.a.Lp");
+  if (!fail) {
     double *xs = &S.u.a.Lp[0][0];
     double *ldb = &S.u.a.Xr[0][0];  // 2 x kLdBuf doubles (Xr holds 128 x 33)
     const int last = ((D - 1) / kPB) * kPB;
@@ -855,32 +984,6 @@ __global__ void __launch_bounds__(kCoopThreads)
     }
     for (int j = t; j < D; j += kCoopThreads) xbuf[j] = xs[j];
     __syncthreads();
-  } else if (!fail) {
-    const int last = ((D - 1) / kPB) * kPB;
-    for (int k0 = last; k0 >= 0; k0 -= kPB) {
-      const int pb = min(kPB, D - k0);
-      if (warp == 0) {  // x_k = M^T y_k
-        const double *Md = ldiag + static_cast<size_t>(k0 / kPB) * kLdStride;
-        double acc = 0.0;
-#pragma unroll 8
-        for (int r = 0; r < kPB; r++) acc += Md[r * kPB + lane] * ((r < pb) ? xbuf[k0 + r] : 0.0);
-        __syncwarp();
-        yk[lane] = (lane < pb) ? acc : 0.0;
-        if (lane < pb) xbuf[k0 + lane] = acc;
-      }
-      __syncthreads();
-      for (int j = t; j < k0; j += kCoopThreads) {
-        double lv[kPB];
-#pragma unroll
-        for (int c = 0; c < kPB; c++)
-          lv[c] = (c < pb) ? A[static_cast<size_t>(k0 + c) * D + j] : 0.0;
-        double sacc = xbuf[j];
-#pragma unroll
-        for (int c = 0; c < kPB; c++) sacc -= lv[c] * yk[c];
-        xbuf[j] = sacc;
-      }
-      __syncthreads();
-    }
   }
   COOP_TICK(4);
   finish_step<kCoopThreads>(t, fail, D, xbuf, Twc, dx, num_poses, delta_thresh, flags);
