@@ -478,6 +478,130 @@ __global__ void __launch_bounds__(kAccThreads, kAccCtasPerSM) gn_accumulate_kern
 }
 
 // ----------------------------------------------------------------------------------------
+// accumulation kernel, two list entries per lane in packed fp32 (gn_packed.cuh): the one that runs
+// ----------------------------------------------------------------------------------------
+#include "gn_packed.cuh"
+
+#ifndef M3R_ACC_PACKED
+#define M3R_ACC_PACKED 1
+#endif
+#ifndef M3R_ACC2_CTAS
+#define M3R_ACC2_CTAS 2
+#endif
+constexpr int kAcc2CtasPerSM = M3R_ACC2_CTAS;
+// Same rings as gn_accumulate_kernel, but a round is 64 list entries: lane l takes entries l and l + 32
+// of the round as the two halves of its register pairs.
+// A round being twice as long, half the ring depth gives the same look-ahead in list entries, and
+// two CTAs (16 warps) fit an SM again: with one the kernel was latency-bound and slower than scalar.
+#ifndef M3R_ACC2_GATHER_LEAD
+#define M3R_ACC2_GATHER_LEAD 2
+#endif
+constexpr int kGather2Lead = M3R_ACC2_GATHER_LEAD;
+// the entries of round t + lead are read when its gathers are issued, so they must have landed by then:
+// the wait at the top of round t completes the groups up to round t - lead, hence entry lead = 2 x lead
+constexpr int kEntry2Lead = 2 * kGather2Lead;
+constexpr int kEnt2Slots = kEntry2Lead + 1, kRec2Slots = kGather2Lead + 1;  // live rounds
+struct __align__(16) AccWarpSmem2 {
+  int ent[kEnt2Slots][3][64];     // [slot][k | idx | q bits][entry of the round]
+  float4 rec[kRec2Slots][2][64];  // [slot][Xj | Xi][entry of the round]
+};
+constexpr int kAcc2SmemBytes = kAccWarps * static_cast<int>(sizeof(AccWarpSmem2));
+static_assert(kSeg % 64 == 0, "a warp segment is a whole number of 64-entry rounds");
+
+template <int KIND>
+__global__ void __launch_bounds__(kAccThreads, kAcc2CtasPerSM) gn_accumulate2_kernel(const AccArgs A) {
+  if (A.flags[0]) return;  // converged earlier: nothing to do
+  extern __shared__ __align__(16) unsigned char acc_smem_raw[];
+  __shared__ double red[kAccWarps][kNAcc];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  AccWarpSmem2 &W = reinterpret_cast<AccWarpSmem2 *>(acc_smem_raw)[warp];
+  const int n = A.n;
+  const int items = A.num_shard_edges * A.chunks_per_edge;
+
+  GnParams P = A.P_;
+  if (KIND == M3R_GN_CALIB) {  // intrinsics live on the device (gn_kernels.cu:1274-1279)
+    P.fx = __ldg(A.K + 0), P.fy = __ldg(A.K + 4), P.cx = __ldg(A.K + 2), P.cy = __ldg(A.K + 5);
+  }
+
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int le = item / A.chunks_per_edge;  // edge within the shard
+    const int e = A.edge_begin + le;
+    const int ix = A.pose_i[e], jx = A.pose_j[e];
+    const Pose2 Tij(rel_sim3(load_pose(A.Twc, ix), load_pose(A.Twc, jx)));
+    const float4 *Pi = A.P + static_cast<size_t>(ix) * n;
+    const float4 *Pj = A.P + static_cast<size_t>(jx) * n;
+    const size_t slot = (static_cast<size_t>(item) * kAccWarps + warp) * kSeg;
+    const int cnt = A.counts[item * kAccWarps + warp];
+    const int nr = (cnt + 63) >> 6;
+    // a round's entries are three 256-byte rows: lanes 0-15 copy the k row, 16-31 the idx row, and
+    // lanes 0-15 the q row with a second instruction (16 B each)
+    const int c4 = (lane & 15) * 4;
+    const int *esrc01 = (lane < 16 ? A.ck : A.cidx) + slot + c4;
+    const int *esrc2 = reinterpret_cast<const int *>(A.cq) + slot + c4;
+
+    F2 acc[kNAcc];
+#pragma unroll
+    for (int k = 0; k < kNAcc; k++) acc[k] = F2(0.f);
+
+    for (int t = -kEntry2Lead; t < nr; t++) {
+      asm volatile("cp.async.wait_group %0;" ::"n"(kGather2Lead - 1) : "memory");
+      __syncwarp();
+      if (t + kEntry2Lead < nr) {
+        const int sl = (t + kEntry2Lead) % kEnt2Slots;
+        cp_async16(&W.ent[sl][lane >> 4][c4], esrc01 + (t + kEntry2Lead) * 64);
+        if (lane < 16) cp_async16(&W.ent[sl][2][c4], esrc2 + (t + kEntry2Lead) * 64);
+      }
+      const int tg = t + kGather2Lead;
+      if (tg >= 0 && tg < nr) {
+        const int sl = tg % kEnt2Slots, rs = tg % kRec2Slots;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int x = h * 32 + lane;
+          const bool in = tg * 64 + x < cnt;
+          const int kk = in ? W.ent[sl][0][x] : 0;
+          const int ii = in ? W.ent[sl][1][x] : 0;
+          cp_async16_ca(&W.rec[rs][0][x], Pj + kk);
+          cp_async16_ca(&W.rec[rs][1][x], Pi + ii);
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      if (t >= 0 && t * 64 + lane < cnt) {  // the first half exists; the second may not (last round)
+        const int sl = t % kEnt2Slots, rs = t % kRec2Slots;
+        const bool in1 = t * 64 + 32 + lane < cnt;
+        const float4 xj0 = W.rec[rs][0][lane], xi0 = W.rec[rs][1][lane];
+        float4 xj1 = W.rec[rs][0][32 + lane], xi1 = W.rec[rs][1][32 + lane];
+        float q1 = __int_as_float(W.ent[sl][2][32 + lane]);
+        if (!in1) {  // harmless inputs and a zero confidence: all weights of that half are zero
+          xj1 = make_float4(0.f, 0.f, 1.f, 0.f), xi1 = xj1, q1 = 0.f;
+        }
+        const F2 Xi[3] = {F2(xi0.x, xi1.x), F2(xi0.y, xi1.y), F2(xi0.z, xi1.z)};
+        const F2 Xj[3] = {F2(xj0.x, xj1.x), F2(xj0.y, xj1.y), F2(xj0.z, xj1.z)};
+        const F2 q(__int_as_float(W.ent[sl][2][lane]), q1);
+        Residual2<KIND>::point(P, Tij, Xi, Xj, q, W.ent[sl][1][lane], in1 ? W.ent[sl][1][32 + lane] : 0, acc);
+      }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+
+    // the two halves meet, then the warp tree in fp32, then fp64 across warps in a fixed order
+#pragma unroll
+    for (int k = 0; k < kNAcc; k++) {
+      float v = acc[k].v.x + acc[k].v.y;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+      if (lane == 0) red[warp][k] = static_cast<double>(v);
+    }
+    __syncthreads();
+    if (threadIdx.x < kNAcc) {
+      double s = 0.0;
+#pragma unroll
+      for (int wq = 0; wq < kAccWarps; wq++) s += red[wq][threadIdx.x];
+      A.partials[static_cast<size_t>(item) * kNAcc + threadIdx.x] = s;
+    }
+    __syncthreads();
+  }
+}
+
+// ----------------------------------------------------------------------------------------
 // per-edge finalisation: S = sum of chunk partials (fixed order), H_jj = A S A^T, g_j = A s
 // ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(64)
@@ -1465,11 +1589,21 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
     a.flags = ws->flags;
     a.n = n, a.edge_begin = prob->edge_begin, a.num_shard_edges = ES, a.chunks_per_edge = chunks;
     a.P_ = make_params(prob);
+#if M3R_ACC_PACKED
+    const size_t cap = static_cast<size_t>(kNumSMs) * kAcc2CtasPerSM;
+#else
     const size_t cap = static_cast<size_t>(kNumSMs) * kAccCtasPerSM;
+#endif
     const int grid = static_cast<int>(items < cap ? items : cap);
     static bool attr_set_dev[64] = {false};  // per device; benign race: idempotent
     bool &attr_set = attr_set_dev[ws->device & 63];
     if (!attr_set) {
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate2_kernel<M3R_GN_RAYS>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kAcc2SmemBytes));
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate2_kernel<M3R_GN_CALIB>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kAcc2SmemBytes));
+      M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate2_kernel<M3R_GN_POINTS>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kAcc2SmemBytes));
       M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_kernel<M3R_GN_RAYS>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kAccSmemBytes));
       M3R_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_kernel<M3R_GN_CALIB>,
@@ -1478,12 +1612,21 @@ extern "C" int m3r_gn_linearize(m3r_gn_workspace *ws, const m3r_gn_problem *prob
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kAccSmemBytes));
       attr_set = true;
     }
+#if M3R_ACC_PACKED
+    if (prob->kind == M3R_GN_RAYS)
+      gn_accumulate2_kernel<M3R_GN_RAYS><<<grid, kAccThreads, kAcc2SmemBytes, s>>>(a);
+    else if (prob->kind == M3R_GN_CALIB)
+      gn_accumulate2_kernel<M3R_GN_CALIB><<<grid, kAccThreads, kAcc2SmemBytes, s>>>(a);
+    else
+      gn_accumulate2_kernel<M3R_GN_POINTS><<<grid, kAccThreads, kAcc2SmemBytes, s>>>(a);
+#else
     if (prob->kind == M3R_GN_RAYS)
       gn_accumulate_kernel<M3R_GN_RAYS><<<grid, kAccThreads, kAccSmemBytes, s>>>(a);
     else if (prob->kind == M3R_GN_CALIB)
       gn_accumulate_kernel<M3R_GN_CALIB><<<grid, kAccThreads, kAccSmemBytes, s>>>(a);
     else
       gn_accumulate_kernel<M3R_GN_POINTS><<<grid, kAccThreads, kAccSmemBytes, s>>>(a);
+#endif
     M3R_LAUNCH_CHECK("gn_accumulate_kernel");
 
     gn_edge_finalize_kernel<<<ES, 64, 0, s>>>(ws->partials.p, prob->Twc, ws->pose_i.p,
