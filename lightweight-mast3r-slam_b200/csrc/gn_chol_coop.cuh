@@ -471,6 +471,63 @@ struct CoopSmem {
 };
 constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
 
+// T = X X^T for the first 32 rows X of the L21 this CTA has just computed: the update the NEXT panel's
+// diagonal block needs.  Run by warps 4, 5, 6, 7 (one per scheduler) of the CTA of the first rows when their own work of
+// the step is over (slot = 0..3), out of rows 0..31 of S.u.a.Lp (the TRSM warp of those rows stages them there); 64 register
+// tiles of 4x4 outputs (rows tr + 8i, columns tc + 8k: consecutive threads read consecutive rows, whose
+// 272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner dimension, two
+// accumulators per output; the halves meet in shared memory and leave through S.Ad, coalesced.
+__device__ __forceinline__ void coop_next_diag_update(CoopSmem &S, double *__restrict__ dT, int slot, int lane) {
+  const int u = slot * 32 + lane;
+  const int tile = u & 63, half = u >> 6;
+  const int tr = tile >> 3, tc = tile & 7;
+  double acc[4][4], acc1[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int k = 0; k < 4; k++) acc[i][k] = 0.0, acc1[i][k] = 0.0;
+  asm volatile("bar.sync 6, 160;");  // the rows are staged
+#pragma unroll 4
+  for (int j = half * (kPB / 2); j < (half + 1) * (kPB / 2); j += 2) {
+    double2 av[4], bv[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      av[i] = *reinterpret_cast<const double2 *>(&S.u.a.Lp[tr + 8 * i][j]);
+      bv[i] = *reinterpret_cast<const double2 *>(&S.u.a.Lp[tc + 8 * i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        acc[i][k] = fma(av[i].x, bv[k].x, acc[i][k]);
+        acc1[i][k] = fma(av[i].y, bv[k].y, acc1[i][k]);
+      }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int k = 0; k < 4; k++) acc[i][k] += acc1[i][k];
+  if (half == 1) {
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) S.dpart[(i * 4 + k) * 64 + tile] = acc[i][k];
+  }
+  asm volatile("bar.sync 3, 128;");
+  if (half == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) S.Ad[tr + 8 * i][tc + 8 * k] = acc[i][k] + S.dpart[(i * 4 + k) * 64 + tile];
+  }
+  asm volatile("bar.sync 3, 128;");
+#pragma unroll
+  for (int i = 0; i < kPB * kPB / 128; i++) {
+    const int x = u + i * 128;
+    dT[x] = S.Ad[x / kPB][x % kPB];
+  }
+}
+
 // Backward substitution L^T x = y for large systems, all CTAs (see the call site).  Out of line: it runs
 // once per solve and must not take part in the register allocation of the panel loop.
 __device__ __noinline__ void coop_backward_multi(cg::grid_group &grid, CoopSmem &S, double *__restrict__ A,
@@ -591,6 +648,7 @@ __global__ void __launch_bounds__(kCoopThreads)
   const int lane = t & 31, warp = t >> 5;
   double *A = sys;
   double *rhs = sys + static_cast<size_t>(D) * D;
+  double *dT = ldiag + static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride;  // kPB x kPB scratch behind the blocks
   if (t == 0) bad = 0;
 #ifdef M3R_COOP_PROF
   long long prof_acc[6] = {0, 0, 0, 0, 0, 0};
@@ -605,12 +663,11 @@ __global__ void __launch_bounds__(kCoopThreads)
   // roots and scaled columns behind it (same scheduler as the chain, whose instructions are sparse; on
   // scheduler 3 it queued behind the DFMAs of the inverse and needed 700 cycles per group of four
   // columns), 1, 2 = the CTA's 64 panel rows (look-ahead update, TRSM, rhs), 3 = inverse of the block
-  // (CTA of the first rows only), 5 = forward-substitution chain y_k, 6, 7 = store the rows of L21
+  // (CTA of the first rows only), 5 = forward-substitution chain y_k; 0 and 3 then store the rows of L21;
+  // 4, 5, 6, 7 of the CTA of the first rows (one per scheduler): diagonal update of the NEXT panel once
+  // their own work is done
   const bool trsm_warp = warp >= 1 && warp <= kTrsmWarps;  // warps 1, 2: schedulers 1, 2
   const int trsm_slot = warp - 1;
-  // diagonal-block update on schedulers 0 and 3 only: 1 and 2 belong to the look-ahead fold of the TRSM
-  // warps (1024 DFMA per row) at that moment; with warp 5 in this group the update took 1.5 us and the fold 2.6
-  const bool diag_warp = (warp & 3) == 0 || (warp & 3) == 3;  // warps 0, 4, 3, 7
 
   for (int k0 = 0; k0 < D; k0 += kPB) {
     const int pb = min(kPB, D - k0);
@@ -629,6 +686,8 @@ __global__ void __launch_bounds__(kCoopThreads)
 #endif
       const int row0 = k0 + pb + rc * kTrsmRows;
       const int nrows = max(0, min(kTrsmRows, D - row0));
+      // the CTA of the first rows prepares the next panel's diagonal update (those rows ARE its Ls)
+      const bool need_T = rc == 0 && k0 + pb < D;
       double (*L11)[kPB + 1] = S.L11;
       double *dinv = S.dinv;
       volatile int *prog = &S.prog;  // pivots of this panel's POTRF published so far
@@ -638,7 +697,7 @@ __global__ void __launch_bounds__(kCoopThreads)
       //    the critical path then; since the factorisation warp carries the chain only, the row path
       //    -- loads, look-ahead fold, TRSM -- is, and a second round trip in front of it costs 1 us per panel.)
       {
-        double vd[kPB * kPB / kCoopThreads], vs[kPB * kPB / kCoopThreads];
+        double vd[kPB * kPB / kCoopThreads], vs[kPB * kPB / kCoopThreads], vt[kPB * kPB / kCoopThreads];
         double vx[kTrsmRows * kPB / kCoopThreads], vl[kTrsmRows * kPB / kCoopThreads];
 #pragma unroll
         for (int i = 0; i < kPB * kPB / kCoopThreads; i++) {
@@ -647,6 +706,7 @@ __global__ void __launch_bounds__(kCoopThreads)
           const size_t g = static_cast<size_t>(k0 + r) * D;
           vd[i] = (r >= pb && r == c) ? 1.0 : 0.0;  // identity on the padding of the last panel
           if (r < pb && c <= r) vd[i] = A[g + k0 + c];
+          vt[i] = (la && r < pb && c <= r) ? dT[x] : 0.0;  // subtracted below: no arithmetic between the loads
           vs[i] = (la && r < pb) ? A[g + kp + c] : 0.0;
         }
 #pragma unroll
@@ -662,7 +722,7 @@ __global__ void __launch_bounds__(kCoopThreads)
 #pragma unroll
         for (int i = 0; i < kPB * kPB / kCoopThreads; i++) {
           const int x = t + i * kCoopThreads;
-          S.Ad[x / kPB][x % kPB] = vd[i];
+          S.Ad[x / kPB][x % kPB] = vd[i] - vt[i];
           S.Ls[x / kPB][x % kPB] = vs[i];
         }
 #pragma unroll
@@ -677,62 +737,9 @@ __global__ void __launch_bounds__(kCoopThreads)
 #ifdef M3R_COOP_PROF
       if (blockIdx.x == 0 && t == 32) tprof_t = clock64();
 #endif
-      // 2. diagonal block -= Ls Ls^T.  128 threads: 64 register tiles of 4x4 outputs (rows
-      //    tr + 8i, columns tc + 8k: consecutive threads read consecutive rows of Ls, whose
-      //    272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner
-      //    dimension; the halves meet in shared memory.  Entries above the diagonal receive
-      //    garbage and are never read.  (The first version gave every thread 4 outputs of one
-      //    row: 5 shared loads per 4 DFMA, 4.2 us per panel on the critical path.)
-      if (la && diag_warp) {
-        // two accumulators per output (even and odd columns of Ls): the dependent DFMA chain is
-        // what this step costs (fp64 latency, not issue), and it halves
-        double acc[4][4], acc1[4][4];
-        const int u = ((warp == 0) ? 0 : (warp == 4) ? 1 : (warp == 3) ? 2 : 3) * 32 + lane;
-        const int tile = u & 63, half = u >> 6;
-        const int tr = tile >> 3, tc = tile & 7;
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-#pragma unroll
-          for (int k = 0; k < 4; k++) acc[i][k] = 0.0, acc1[i][k] = 0.0;
-#pragma unroll 4
-        for (int j = half * (kPB / 2); j < (half + 1) * (kPB / 2); j += 2) {
-          double2 av[4], bv[4];
-#pragma unroll
-          for (int i = 0; i < 4; i++) {
-            av[i] = *reinterpret_cast<const double2 *>(&S.Ls[tr + 8 * i][j]);
-            bv[i] = *reinterpret_cast<const double2 *>(&S.Ls[tc + 8 * i][j]);
-          }
-#pragma unroll
-          for (int i = 0; i < 4; i++)
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-              acc[i][k] = fma(av[i].x, bv[k].x, acc[i][k]);
-              acc1[i][k] = fma(av[i].y, bv[k].y, acc1[i][k]);
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-#pragma unroll
-          for (int k = 0; k < 4; k++) acc[i][k] += acc1[i][k];
-        if (half == 1) {
-#pragma unroll
-          for (int i = 0; i < 4; i++)
-#pragma unroll
-            for (int k = 0; k < 4; k++) S.dpart[(i * 4 + k) * 64 + tile] = acc[i][k];
-        }
-        asm volatile("bar.sync 3, 128;");  // warps 0, 4, 3, 7
-        if (half == 0) {
-#pragma unroll
-          for (int i = 0; i < 4; i++)
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-              S.Ad[tr + 8 * i][tc + 8 * k] -= acc[i][k] + S.dpart[(i * 4 + k) * 64 + tile];
-        }
-        asm volatile("bar.sync 3, 128;");  // the updated diagonal block is complete
-#ifdef M3R_FOLD_AFTER_DIAG
-        asm volatile("bar.arrive 6, 192;");
-#endif
-      }
+      // 2. (the update of the diagonal block by the previous panel, 1.5 us in front of the chain, is no
+      //    longer done here: CTA 0 computed T = L21_top L21_top^T at the end of the previous step, when
+      //    four of its warps were idle, and the loads above subtracted it -- coop_next_diag_update)
       COOP_ATICK(9);
       if (warp == 0) {
         // 3. POTRF, elimination chain (rows in registers); warp 4 scales the columns behind it
@@ -742,11 +749,14 @@ __global__ void __launch_bounds__(kCoopThreads)
         COOP_STAMP(0);
         if (warp_chol32_chain(a, lane, S.U, &S.prog_u) && lane == 0) bad = 1;  // step discarded
         COOP_STAMP(1);
+        asm volatile("bar.sync 5, 128;");  // the TRSM warps have staged their rows of L21
+        coop_store_rows(A, D, k0, pb, row0, nrows, S.u.a.Xr, 1, lane);
         COOP_ATICK(10);
       } else if (warp == 4) {
         COOP_STAMP(2);
         warp_chol32_scale(S.U, lane, dinv, L11, &S.prog_u, prog);  // publishes L11 / dinv, four columns at a time
         COOP_STAMP(3);
+        if (need_T) coop_next_diag_update(S, dT, 0, lane);
       } else if (trsm_warp) {
         // 4. this thread's row: fold in the previous panel's update while warp 0 factors
         const int r = trsm_slot * 32 + lane;
@@ -755,9 +765,6 @@ __global__ void __launch_bounds__(kCoopThreads)
         double x[kPB];
 #pragma unroll
         for (int c = 0; c < kPB; c++) x[c] = S.u.a.Xr[r][c];
-#ifdef M3R_FOLD_AFTER_DIAG
-        if (la) asm volatile("bar.sync 6, 192;");  // experiment: the fold starts when the diagonal update is done
-#endif
         if (la) {
 #pragma unroll 2
           for (int j = 0; j < kPB; j += 2) {
@@ -789,7 +796,14 @@ __global__ void __launch_bounds__(kCoopThreads)
         // staged, the two spare warps store whole rows, one coalesced instruction per row
 #pragma unroll
         for (int c = 0; c < kPB; c++) S.u.a.Xr[r][c] = x[c];  // this thread's own slots
-        asm volatile("bar.arrive 5, 128;");  // warps 6 and 7 store them; this warp goes on to the rhs
+        asm volatile("bar.arrive 5, 128;");  // warps 0 and 3 store them; this warp goes on to the rhs
+        if (need_T && trsm_slot == 0) {
+          // rows 0..31 are the next panel's Ls: staged for coop_next_diag_update where only this warp
+          // has been reading (its own rows of Lp, in the fold; S.Ls may still be read by the other TRSM warp)
+#pragma unroll
+          for (int c = 0; c < kPB; c++) S.u.a.Lp[r][c] = x[c];
+          asm volatile("bar.arrive 6, 160;");
+        }
         COOP_TTICK(2);
         if (warp == 1) COOP_STAMP(6);
         asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));  // y_k ready
@@ -811,11 +825,12 @@ __global__ void __launch_bounds__(kCoopThreads)
           coop_invert_block(L11, dinv, ldiag + static_cast<size_t>(k0 / kPB) * kLdStride, lane, prog);
           COOP_STAMP(8);
         }
-      } else if (warp == 6 || warp == 7) {
         asm volatile("bar.sync 5, 128;");  // the TRSM warps have staged their rows of L21
-        if (warp == 6) COOP_STAMP(10);
-        coop_store_rows(A, D, k0, pb, row0, nrows, S.u.a.Xr, warp == 6 ? 0 : 1, lane);
-        if (warp == 6) COOP_STAMP(11);
+        COOP_STAMP(10);
+        coop_store_rows(A, D, k0, pb, row0, nrows, S.u.a.Xr, 0, lane);
+        COOP_STAMP(11);
+      } else if (warp == 6 || warp == 7) {
+        if (need_T) coop_next_diag_update(S, dT, warp == 6 ? 2 : 3, lane);
       } else if (warp == 5) {
         // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp and one pivot
         //    behind it: step c needs L11[.][c] and dinv[c] only
@@ -832,6 +847,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         COOP_STAMP(7);
         asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));
         if (rc == 0 && lane < pb) xbuf[k0 + lane] = mine;
+        if (need_T) coop_next_diag_update(S, dT, 1, lane);
       }
       __syncthreads();
       if (warp == 0) COOP_STAMP(9);
