@@ -705,9 +705,9 @@ def gn_report(be, g, D, kind, rank, world, peak, refmod, reps=3, nccl_too=True, 
         "gpu_launches": int(launches), "system_unknowns": 7 * (N - 1),
         "edges_per_rank": E // world,
         "exchange": "none" if world == 1 else "NVLink peer memory (m3r_gn_comm_*), fp64 system",
-        "roofline": {"bound": "hbm", "kernel": f"gn_accumulate_kernel<{kind}> (+ edge finalize + assemble)",
+        "roofline": {"bound": "hbm", "kernel": f"gn_accumulate2_kernel<{kind}> (+ edge finalize + assemble)",
                      "achieved": lin_gbs, "peak": peak, "unit": "GB/s", "frac": lin_gbs / peak,
-                     "traffic": traffic("gn_accumulate_kernel") if (kind == "rays" and N == 64 and world == 1) else None,
+                     "traffic": traffic("gn_accumulate2_kernel") if (kind == "rays" and N == 64 and world == 1) else None,
                      "bytes_per_iter": gn_bytes,
                      "note": "algorithmic = 45 B x E x n per iteration (SURVEY 8d) / ranks; the kernel reads "
                              "compacted lists and hits L2 on the pointmaps, so DRAM traffic is below it",
