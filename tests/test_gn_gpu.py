@@ -248,6 +248,35 @@ def test_failed_factorisation_gives_zero_step(backends):
         assert (dx == 0).all() and torch.equal(Twc.cpu(), g["Twc_init"])
 
 
+@pytest.mark.parametrize("N", [75, 76, 111, 148])
+def test_solver_backward_substitution_on_all_ctas(N):
+    """D = 518, 525, 770, 1029: just above the size (512) from which the backward substitution runs on
+    all CTAs in super-blocks of 256 columns -- a last super-block of 6 and 13 columns, a whole number of
+    panels but a partial super-block, and five super-blocks with a partial last panel.  The solver is held
+    to the fp64 solution of the system it was handed."""
+    assert _solve_vs_fp64_of_same_system(N) < 1e-5
+
+
+@pytest.mark.parametrize("N", [70, 80])
+def test_failed_factorisation_in_a_late_panel(N):
+    """One keyframe without any valid match: its 7x7 block of H is zero, the pivot in panel 3 of the
+    blocked factorisation is not usable (single-CTA and all-CTA backward substitution paths), the step is
+    discarded: dx = 0, Twc untouched, nothing NaN (gn_kernels.cu:147-150)."""
+    g = synth.make_graph(N, 24, 32, seed=6)
+    dead = 15  # keyframe 15 -> unknowns 98..104 (panel 3)
+    touch = (g["ii"] == dead) | (g["jj"] == dead)
+    g["valid_match"] = g["valid_match"].clone()
+    g["valid_match"][touch] = 0
+    Twc = g["Twc_init"].cuda().clone()
+    gn = _staged("rays", g, Twc)
+    gn.begin()
+    gn.linearize()
+    gn.solve_retract(0.0)
+    torch.cuda.synchronize()
+    assert torch.isfinite(gn.dx).all() and (gn.dx == 0).all()
+    assert torch.equal(Twc.cpu(), g["Twc_init"])
+
+
 def test_early_stop_and_iteration_count(backends):
     g = synth.make_graph(4, 48, 64, seed=4)
     Twc = g["Twc_init"].cuda().clone()
