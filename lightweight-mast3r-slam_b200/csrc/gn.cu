@@ -1506,7 +1506,7 @@ extern "C" int m3r_gn_begin(m3r_gn_workspace *ws, const m3r_gn_problem *prob, vo
     if ((rc = ws->edge_H.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 49))) return rc;
     if ((rc = ws->edge_g.reserve(static_cast<size_t>(ES > 0 ? ES : 1) * 7))) return rc;
     if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
-    if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride + kPB * kPB))) return rc;
+    if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride + 2 * kPB * kPB))) return rc;
   }
   {
     // 4 points per thread in flight; keyframes in grid.y (at most 512 keyframe slots, frame.py:221)
@@ -1659,7 +1659,7 @@ extern "C" int m3r_gn_solve_retract(m3r_gn_workspace *ws, const m3r_gn_problem *
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int D = 7 * (prob->num_poses - 1);
   if ((rc = ws->xbuf.reserve(static_cast<size_t>(D)))) return rc;
-  if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride + kPB * kPB))) return rc;
+  if ((rc = ws->ldiag.reserve(static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride + 2 * kPB * kPB))) return rc;
 #ifdef M3R_TEST_VARIANTS
   // variants build only (tests/_variants): M3R_GN_SOLVER = cluster (D <= 448; measured slower: 430
   // vs 340 us at D = 441, profiles/r1_d_cluster_solver_phases.txt) | multi (one launch per panel

@@ -476,7 +476,7 @@ constexpr int kCoopSmemBytes = static_cast<int>(sizeof(CoopSmem));
 // the step is over (slot = 0..3), out of rows 0..31 of S.u.a.Lp (the TRSM warp of those rows stages them there); 64 register
 // tiles of 4x4 outputs (rows tr + 8i, columns tc + 8k: consecutive threads read consecutive rows, whose
 // 272-byte stride makes the 128-bit loads conflict-free) x 2 halves of the inner dimension, two
-// accumulators per output; the halves meet in shared memory and leave through S.Ad, coalesced.
+// accumulators per output.
 __device__ __forceinline__ void coop_next_diag_update(CoopSmem &S, double *__restrict__ dT, int slot, int lane) {
   const int u = slot * 32 + lane;
   const int tile = u & 63, half = u >> 6;
@@ -507,25 +507,17 @@ __device__ __forceinline__ void coop_next_diag_update(CoopSmem &S, double *__res
   for (int i = 0; i < 4; i++)
 #pragma unroll
     for (int k = 0; k < 4; k++) acc[i][k] += acc1[i][k];
-  if (half == 1) {
+  // The two halves of the inner dimension meet in global memory: fire-and-forget fp64 adds (RED) into a
+  // zeroed T.  Two addends per entry: the sum does not depend on their order.  (Combining them through
+  // shared memory, two named barriers and a staged copy was ~100 dependent instructions: 0.8 us at the
+  // very end of the step.)
 #pragma unroll
-    for (int i = 0; i < 4; i++)
+  for (int i = 0; i < 4; i++)
 #pragma unroll
-      for (int k = 0; k < 4; k++) S.dpart[(i * 4 + k) * 64 + tile] = acc[i][k];
-  }
-  asm volatile("bar.sync 3, 128;");
-  if (half == 0) {
-#pragma unroll
-    for (int i = 0; i < 4; i++)
-#pragma unroll
-      for (int k = 0; k < 4; k++) S.Ad[tr + 8 * i][tc + 8 * k] = acc[i][k] + S.dpart[(i * 4 + k) * 64 + tile];
-  }
-  asm volatile("bar.sync 3, 128;");
-#pragma unroll
-  for (int i = 0; i < kPB * kPB / 128; i++) {
-    const int x = u + i * 128;
-    dT[x] = S.Ad[x / kPB][x % kPB];
-  }
+    for (int k = 0; k < 4; k++) {
+      const int r = tr + 8 * i, c = tc + 8 * k;
+      if (c <= r) atomicAdd(&dT[r * kPB + c], acc[i][k]);
+    }
 }
 
 // Backward substitution L^T x = y for large systems, all CTAs (see the call site).  Out of line: it runs
@@ -648,7 +640,10 @@ __global__ void __launch_bounds__(kCoopThreads)
   const int lane = t & 31, warp = t >> 5;
   double *A = sys;
   double *rhs = sys + static_cast<size_t>(D) * D;
-  double *dT = ldiag + static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride;  // kPB x kPB scratch behind the blocks
+  // two kPB x kPB scratch blocks behind the diagonal blocks: panel p reads T from block p & 1 and CTA 0
+  // builds the next one in block (p + 1) & 1, which it zeroes at the start of the step (its last
+  // readers were the loads of panel p - 1, a grid barrier ago)
+  double *dT2 = ldiag + static_cast<size_t>((D + kPB - 1) / kPB) * kLdStride;
   if (t == 0) bad = 0;
 #ifdef M3R_COOP_PROF
   long long prof_acc[6] = {0, 0, 0, 0, 0, 0};
@@ -688,6 +683,12 @@ __global__ void __launch_bounds__(kCoopThreads)
       const int nrows = max(0, min(kTrsmRows, D - row0));
       // the CTA of the first rows prepares the next panel's diagonal update (those rows ARE its Ls)
       const bool need_T = rc == 0 && k0 + pb < D;
+      const double *dT = dT2 + ((k0 / kPB) & 1) * (kPB * kPB);
+      double *dTn = dT2 + (((k0 / kPB) + 1) & 1) * (kPB * kPB);
+      if (need_T) {
+#pragma unroll
+        for (int i = 0; i < kPB * kPB / kCoopThreads; i++) dTn[t + i * kCoopThreads] = 0.0;
+      }
       double (*L11)[kPB + 1] = S.L11;
       double *dinv = S.dinv;
       volatile int *prog = &S.prog;  // pivots of this panel's POTRF published so far
@@ -756,7 +757,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         COOP_STAMP(2);
         warp_chol32_scale(S.U, lane, dinv, L11, &S.prog_u, prog);  // publishes L11 / dinv, four columns at a time
         COOP_STAMP(3);
-        if (need_T) coop_next_diag_update(S, dT, 0, lane);
+        if (need_T) coop_next_diag_update(S, dTn, 0, lane);
       } else if (trsm_warp) {
         // 4. this thread's row: fold in the previous panel's update while warp 0 factors
         const int r = trsm_slot * 32 + lane;
@@ -830,7 +831,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         coop_store_rows(A, D, k0, pb, row0, nrows, S.u.a.Xr, 0, lane);
         COOP_STAMP(11);
       } else if (warp == 6 || warp == 7) {
-        if (need_T) coop_next_diag_update(S, dT, warp == 6 ? 2 : 3, lane);
+        if (need_T) coop_next_diag_update(S, dTn, warp == 6 ? 2 : 3, lane);
       } else if (warp == 5) {
         // 5. y_k = L11^-1 b_k (serial chain over the pivots), off the POTRF warp and one pivot
         //    behind it: step c needs L11[.][c] and dinv[c] only
@@ -847,7 +848,7 @@ __global__ void __launch_bounds__(kCoopThreads)
         COOP_STAMP(7);
         asm volatile("bar.sync 2, %0;" ::"n"(kTrsmRows + 32));
         if (rc == 0 && lane < pb) xbuf[k0 + lane] = mine;
-        if (need_T) coop_next_diag_update(S, dT, 1, lane);
+        if (need_T) coop_next_diag_update(S, dTn, 1, lane);
       }
       __syncthreads();
       if (warp == 0) COOP_STAMP(9);
