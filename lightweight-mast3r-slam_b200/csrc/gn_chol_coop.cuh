@@ -1,20 +1,24 @@
 // One cooperative kernel per Gauss-Newton iteration for the linear step:
 // blocked right-looking fp64 Cholesky of the dense system (resident in L2), forward
 // substitution fused into the panel phase, backward substitution, dx = -x, retraction and the
-// stop test.  Replaces 2*ceil(D/32)+1 dependent launches by one launch with two grid-wide
-// barriers per 32-column panel.  (Included by gn.cu inside namespace m3r.)
+// stop test.  Replaces 2*ceil(D/32)+1 dependent launches by one launch with ONE grid-wide
+// barrier per 32-column panel.  (Included by gn.cu inside namespace m3r.)
 //
-// Per panel k (columns k0..k0+pb), ONE grid barrier per panel (look-ahead):
-//   phase A  (panel CTAs: one per 128 rows below the panel)  folds the previous panel's
-//            trailing update into this panel's columns while loading them, factors the
-//            pb x pb diagonal block redundantly (one warp, rows in registers, shuffles; no
-//            barrier between POTRF and TRSM), solves y_k = L11^-1 b_k, then its rows:
-//            L21 = A21 L11^-T, b_r -= L21 y_k.  CTA 0 stores L11 to `ldiag`.
+// Per panel k (columns k0..k0+pb), look-ahead by one panel:
+//   phase A  (panel CTAs: one per 64 rows below the panel; the warps of a CTA have roles, see the
+//            kernel)  loads the diagonal block minus T (the previous panel's update of it, prepared at
+//            the end of the previous step) and its rows, folds the previous panel's trailing update
+//            into those rows, factors the pb x pb diagonal block redundantly -- one warp runs the
+//            elimination chain, another takes the square roots and publishes the scaled columns --
+//            while the TRSM rows (L21 = A21 L11^-T), the forward chain y_k = L11^-1 b_k and the inverse
+//            of the block follow the published columns; b_r -= L21 y_k.  CTA 0 stores L11^-1 to `ldiag`
+//            and computes T for the next panel from the rows it has just solved.
 //   phase B  (all other CTAs, at the same time)  A22 -= L21 L21^T of the PREVIOUS panel on the
-//            rows/columns behind this panel, lower tiles 32x32 or 64x64.
+//            rows/columns behind this panel, lower tiles 32x32 or 64x64, pipelined over the tiles.
 //   grid.sync
-// After the last panel CTA 0 runs the backward substitution L^T x = y (column oriented: every
-// step is one round of independent, coalesced loads) and finish_step().
+// Then the backward substitution L^T x = y: CTA 0 alone for D <= 512 (x in shared memory, the next
+// block's rows in flight), all CTAs in super-blocks of 8 panels above that; finish_step() on CTA 0.
+// What was measured on the way, and what was tried and dropped: profiles/r2_i_potrf_chain.md.
 #pragma once
 
 namespace cg = ::cooperative_groups;  // <cooperative_groups.h> is included by gn.cu at global scope
@@ -451,7 +455,6 @@ struct CoopSmem {
   double Ls[kPB][kLs];       // previous panel's L21, rows of the diagonal block
   double U[kPB][kPB];        // unscaled columns of the factor, U[c][row] (warp_chol32_chain)
   double dinv[kPB], yk[kPB], bk[kPB];
-  double dpart[64 * 16];     // second half of the diagonal-block update (k = 16..31)
   union {
     struct {
       double Xr[kTrsmRows][kPB + 1];  // this CTA's rows of the panel
